@@ -1,0 +1,183 @@
+/* mcpt.h — C ABI of the B200-native hot path of Arieys/MonteCarloPathTracing.
+ *
+ * The reference has no FFI: its hot path sits behind three in-process C++ seams
+ * (citations into /root/reference):
+ *   seam 1  getMortonCode (MTPC/sceneManagement.cpp:179) + std::sort (MTPC/MTPC.cpp:44)
+ *           + BVH::BVH (MTPC/MTPC.cpp:46, MTPC/BVH.cpp:37)          -> mcpt_build_bvh
+ *   seam 2  bool ray_intersect(Ray, scene_data&, BVH&, intersection&)
+ *           (MTPC/pathTracing.h:21, MTPC/pathTracing.cpp:382)       -> mcpt_trace
+ *   seam 3  void generateImg(scene_data&, BVH&, image&, int)
+ *           (MTPC/pathTracing.h:25, MTPC/pathTracing.cpp:274)       -> mcpt_render
+ * and the outer entry point render_scene(path, filename, spp) (MTPC/MTPC.cpp:35) is kept by the
+ * C++ host (montecarlopathtracing_b200/host) and exported here as mcpt_render_scene.
+ *
+ * Conventions: every function returns 0 on success, a negative mcpt_status otherwise;
+ * mcpt_last_error() gives the message (thread-local).  Handles are opaque.  The caller owns all
+ * host buffers; the library owns device memory.  One context = one GPU; one host thread per
+ * context.  Plain pointers and sizes only.  There is NO CPU fallback: without a usable CUDA device
+ * every compute call fails with MCPT_ERR_CUDA.
+ */
+#ifndef MCPT_H
+#define MCPT_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MCPT_API __attribute__((visibility("default")))
+
+typedef enum mcpt_status {
+    MCPT_OK = 0,
+    MCPT_ERR_ARG = -1,     /* bad argument / call order */
+    MCPT_ERR_CUDA = -2,    /* CUDA runtime error, no device, or kernels not built for it */
+    MCPT_ERR_IO = -3,      /* scene file missing / unparsable */
+    MCPT_ERR_NOMEM = -4
+} mcpt_status;
+
+/* ---- scene description (host side, flattened from the reference's scene_data) ------------- */
+
+/* Material (MTPC/sceneManagement.h:123-148). tex_id < 0 = no map_Kd. */
+typedef struct mcpt_material {
+    double kd[3], ks[3];
+    double Ns, Ni;
+    int32_t tex_id;
+    int32_t _pad;
+} mcpt_material;
+
+/* Texture: decoded map_Kd, BGR byte order as cv::imread returns it (MTPC/sceneManagement.h:137). */
+typedef struct mcpt_texture {
+    int32_t height, width;
+    const uint8_t* bgr; /* height*width*3 */
+} mcpt_texture;
+
+/* Light: one per "mtlname" line of the .camera file, in file order (MTPC/sceneManagement.cpp:241-257). */
+typedef struct mcpt_light {
+    int32_t mat_id;
+    int32_t _pad;
+    double radiance[3];
+} mcpt_light;
+
+/* Camera (MTPC/sceneManagement.h:150-156). */
+typedef struct mcpt_camera {
+    double eye[3], lookat[3], up[3];
+    double fovy;
+    int32_t width, height;
+} mcpt_camera;
+
+/* Faces are in OBJ file order (the order of Material::f, i.e. of the light-sampling CDF,
+ * MTPC/sceneManagement.cpp:181-182). pos/nrm: 9 doubles per face (v1 v2 v3); uv: 6 per face. */
+typedef struct mcpt_scene_desc {
+    int32_t n_faces;
+    int32_t n_materials;
+    int32_t n_textures;
+    int32_t n_lights;
+    const double* pos;
+    const double* nrm;
+    const double* uv;
+    const int32_t* mat_id;
+    const mcpt_material* materials;
+    const mcpt_texture* textures;
+    const mcpt_light* lights;
+} mcpt_scene_desc;
+
+/* Closest-hit record of seam 2. tri = face index in OBJ order (-1 = miss); leaf = position in the
+ * Morton-sorted leaf order; (u,v) are the barycentric weights of v2 and v3 (v1 has 1-u-v), i.e.
+ * findGarCor's (b2,b3) (MTPC/pathTracing.cpp:416-428). */
+typedef struct mcpt_hit {
+    float t, u, v;
+    int32_t tri;
+    int32_t leaf;
+} mcpt_hit;
+
+typedef struct mcpt_stats {
+    double samples;        /* camera samples integrated */
+    double rays;           /* closest-hit queries traced (primary + shadow + extend), device-counted */
+    double node_visits;    /* BVH node fetches (only with MCPT_FLAG_COUNT) */
+    double tri_tests;      /* ray/triangle tests (only with MCPT_FLAG_COUNT) */
+    float render_ms;       /* CUDA-event time of the render kernels on the context's stream */
+    float build_ms;        /* last mcpt_build_bvh */
+    int32_t kernel_launches; /* kernels launched by the call (render: integrator + reduce) */
+    float integrate_ms;    /* CUDA-event time of the integrator kernel alone (the dominant kernel) */
+} mcpt_stats;
+
+enum { MCPT_MODE_MEGAKERNEL = 0, MCPT_MODE_WAVEFRONT = 1 };
+enum { MCPT_FLAG_COUNT = 1,            /* count node visits / triangle tests (slower) */
+       MCPT_FLAG_NO_PRIMARY_REUSE = 2  /* re-trace the (identical, Q4) primary ray for every sample */ };
+
+/* Number of sample chunks a render is always cut into; GPU r of R owns chunks [r*C/R,(r+1)*C/R). */
+#define MCPT_NUM_CHUNKS 8
+
+/* ---- host side: the kept C++ shell (loaders, render_scene, PNG) ---------------------------- */
+
+typedef struct mcpt_host_scene mcpt_host_scene;
+
+/* Parse <path><name>.{mtl,obj,camera} with the reference's grammar
+ * (MTPC/sceneManagement.cpp:17-274; CRLF-safe) and flatten to mcpt_scene_desc.  Textures are read
+ * from the "<map_Kd>.bgr" sidecar (int32 rows, int32 cols, BGR bytes), looked up
+ * in the CWD, then <path>, then $MCPT_TEXDIR. */
+MCPT_API int mcpt_scene_load(const char* path, const char* name, mcpt_host_scene** out);
+MCPT_API const mcpt_scene_desc* mcpt_scene_get_desc(const mcpt_host_scene* s);
+MCPT_API const mcpt_camera* mcpt_scene_get_camera(const mcpt_host_scene* s);
+MCPT_API void mcpt_scene_free(mcpt_host_scene* s);
+
+/* render_scene(path, filename, spp) of MTPC/MTPC.cpp:35-68 on cuda device `device`:
+ * load -> upload -> build -> render -> quantise -> <out_dir><name>-SPP<spp>.png
+ * (out_dir NULL = "../result/", the reference's hard-coded directory, MTPC/MTPC.cpp:64). */
+MCPT_API int mcpt_render_scene(const char* path, const char* name, int spp, const char* out_dir, int device);
+
+/* imshow of MTPC/MTPC.cpp:10-33: (uchar)clamp(v*255,0,255), no gamma, uncompressed PNG
+ * (replaces MTPC/svpng.inc:77-108; closes the file). rgb = h*w*3 floats, row 0 on top. */
+MCPT_API int mcpt_write_png(const char* file, const float* rgb, int width, int height);
+
+/* ---- device side --------------------------------------------------------------------------- */
+
+typedef struct mcpt_ctx mcpt_ctx;
+
+MCPT_API const char* mcpt_last_error(void);
+MCPT_API int mcpt_create(int device, mcpt_ctx** out);
+MCPT_API void mcpt_destroy(mcpt_ctx* ctx);
+/* Run on the caller's CUDA stream (a cudaStream_t passed as void*) instead of the context's own. */
+MCPT_API int mcpt_set_stream(mcpt_ctx* ctx, void* cuda_stream);
+/* Philox key salt (default 0). Images depend only on (seed, pixel, sample), never on GPU count. */
+MCPT_API int mcpt_set_seed(mcpt_ctx* ctx, uint64_t seed);
+
+/* H2D copy of the flattened scene; precomputes per-light area CDFs (MTPC/pathTracing.cpp:177-184). */
+MCPT_API int mcpt_upload_scene(mcpt_ctx* ctx, const mcpt_scene_desc* scene);
+
+/* Seam 1. Morton codes (bit-exact with MTPC/morton code.cpp:3-32) -> CUB radix sort of (code, face)
+ * -> Karras radix tree -> bottom-up AABB refit -> traversal layout.  ms_out (may be NULL) = device time. */
+MCPT_API int mcpt_build_bvh(mcpt_ctx* ctx, float* ms_out);
+
+/* Parity hooks for seam 1: n_faces entries each; any pointer may be NULL.
+ * codes_obj_order[i] = code of face i; codes_sorted / face_idx_sorted = the sorted leaf order. */
+MCPT_API int mcpt_get_morton(mcpt_ctx* ctx, uint32_t* codes_obj_order, uint32_t* codes_sorted,
+                             int32_t* face_idx_sorted);
+/* The built tree, for structural tests: n_faces-1 internal nodes x 16 floats
+ * (see DESIGN.md "node layout"); parent[n_faces-1]; root index. */
+MCPT_API int mcpt_get_nodes(mcpt_ctx* ctx, float* nodes16, int32_t* root);
+
+/* Seam 2. Closest hit of n rays, HOST buffers: org_dir = n x 6 floats (origin, direction; the
+ * direction need not be unit).  Tie rule and the d.x==0 quirk follow MTPC/pathTracing.cpp:347-361. */
+MCPT_API int mcpt_trace(mcpt_ctx* ctx, const float* org_dir, int n, mcpt_hit* hits_out, mcpt_stats* stats);
+/* Same with DEVICE buffers (no copies); used to time traversal alone. */
+MCPT_API int mcpt_trace_device(mcpt_ctx* ctx, const float* d_org_dir, int n, mcpt_hit* d_hits_out,
+                               int flags, mcpt_stats* stats);
+
+/* Seam 3. Mean radiance image into HOST rgb_out (height*width*3 floats, row 0 on top), all
+ * MCPT_NUM_CHUNKS sample chunks on this GPU.  width/height override the camera's when > 0. */
+MCPT_API int mcpt_render(mcpt_ctx* ctx, const mcpt_camera* cam, int width, int height, int spp, int mode,
+                         int flags, float* rgb_out, mcpt_stats* stats);
+/* Multi-GPU building block: integrate only chunks [chunk_begin, chunk_end) of the spp samples and
+ * leave their fixed-tree SUM (not mean) in the DEVICE buffer d_partial (height*width*3 floats). */
+MCPT_API int mcpt_render_chunks(mcpt_ctx* ctx, const mcpt_camera* cam, int width, int height, int spp,
+                                int chunk_begin, int chunk_end, int mode, int flags, float* d_partial,
+                                mcpt_stats* stats);
+/* d_out[i] = scale * pairwise_tree_sum_k(d_partials[k*count + i]), k < n (n a power of two <= 8);
+ * the same association as inside mcpt_render, so 1/2/4/8-GPU images are bit-identical. */
+MCPT_API int mcpt_sum_partials(mcpt_ctx* ctx, const float* d_partials, int n, int64_t count, float scale,
+                               float* d_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MCPT_H */

@@ -1,0 +1,11 @@
+"""mcpt-b200: B200-native hot path of Arieys/MonteCarloPathTracing behind its render_scene entry point.
+
+The product is libmcpt.so (hand-written sm_100a CUDA kernels + the C++ host shell, C ABI in
+include/mcpt.h).  This package is the thin Python mirror used by the tests and bench.py.
+"""
+from ._capi import (FLAG_COUNT, FLAG_NO_PRIMARY_REUSE, MODE_MEGAKERNEL, MODE_WAVEFRONT, NUM_CHUNKS, Camera, McptError,
+                    SceneDesc, Stats)
+from .api import Context, HostScene, render_scene, write_png
+
+__all__ = ["Context", "HostScene", "render_scene", "write_png", "Camera", "SceneDesc", "Stats", "McptError", "NUM_CHUNKS",
+           "MODE_MEGAKERNEL", "MODE_WAVEFRONT", "FLAG_COUNT", "FLAG_NO_PRIMARY_REUSE"]

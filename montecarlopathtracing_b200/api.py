@@ -1,0 +1,183 @@
+"""Python mirror of the reference's driver surface (MTPC/MTPC.cpp:35-68) over the C ABI.
+
+HostScene  = scene_data after read_scene (MTPC/sceneManagement.cpp:264), flattened.
+Context    = one GPU: upload -> build_bvh (seam 1) -> trace (seam 2) / render (seam 3).
+All compute happens in libmcpt.so on the GPU; numpy is only the host buffer type.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi as capi
+from ._capi import check, lib
+
+
+def _np_view(ptr, n, dtype):
+    if n == 0:
+        return np.zeros(0, dtype=dtype)
+    return np.ctypeslib.as_array(ptr, shape=(n,)).view(dtype)
+
+
+class HostScene:
+    """Scene files parsed by the C++ host loader (CRLF-safe port of the reference grammar)."""
+
+    def __init__(self, path, name):
+        self._h = C.c_void_p()
+        check(lib().mcpt_scene_load(path.encode(), name.encode(), C.byref(self._h)))
+        self.desc_ptr = lib().mcpt_scene_get_desc(self._h)
+        self.desc = self.desc_ptr.contents
+        self.camera = lib().mcpt_scene_get_camera(self._h).contents
+        d = self.desc
+        n = d.n_faces
+        self.n_faces = n
+        self.pos = _np_view(d.pos, 9 * n, np.float64).reshape(n, 3, 3)
+        self.nrm = _np_view(d.nrm, 9 * n, np.float64).reshape(n, 3, 3)
+        self.uv = _np_view(d.uv, 6 * n, np.float64).reshape(n, 3, 2)
+        self.mat_id = _np_view(d.mat_id, n, np.int32)
+        self.materials = [d.materials[i] for i in range(d.n_materials)]
+        self.lights = [d.lights[i] for i in range(d.n_lights)]
+        self.textures = [d.textures[i] for i in range(d.n_textures)]
+
+    def close(self):
+        if self._h:
+            lib().mcpt_scene_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def make_desc(pos, nrm, uv, mat_id, materials, lights, textures=()):
+    """Build a SceneDesc from numpy arrays (synthetic scenes). Returns (desc, keepalive)."""
+    pos = np.ascontiguousarray(pos, dtype=np.float64).reshape(-1)
+    nrm = np.ascontiguousarray(nrm, dtype=np.float64).reshape(-1)
+    uv = np.ascontiguousarray(uv, dtype=np.float64).reshape(-1)
+    mat_id = np.ascontiguousarray(mat_id, dtype=np.int32)
+    n = mat_id.shape[0]
+    assert pos.size == 9 * n and nrm.size == 9 * n and uv.size == 6 * n
+    mats = (capi.Material * max(len(materials), 1))()
+    for i, m in enumerate(materials):
+        mats[i].kd[:] = m.get("kd", (0, 0, 0)); mats[i].ks[:] = m.get("ks", (0, 0, 0))
+        mats[i].Ns = m.get("Ns", 1.0); mats[i].Ni = m.get("Ni", 1.0); mats[i].tex_id = m.get("tex_id", -1)
+    lts = (capi.Light * max(len(lights), 1))()
+    for i, l in enumerate(lights):
+        lts[i].mat_id = l["mat_id"]; lts[i].radiance[:] = l["radiance"]
+    texs = (capi.Texture * max(len(textures), 1))()
+    tex_keep = []
+    for i, t in enumerate(textures):
+        a = np.ascontiguousarray(t, dtype=np.uint8)
+        tex_keep.append(a)
+        texs[i].height, texs[i].width = a.shape[0], a.shape[1]
+        texs[i].bgr = a.ctypes.data_as(C.POINTER(C.c_uint8))
+    d = capi.SceneDesc()
+    d.n_faces, d.n_materials, d.n_textures, d.n_lights = n, len(materials), len(textures), len(lights)
+    d.pos = pos.ctypes.data_as(C.POINTER(C.c_double)); d.nrm = nrm.ctypes.data_as(C.POINTER(C.c_double))
+    d.uv = uv.ctypes.data_as(C.POINTER(C.c_double)); d.mat_id = mat_id.ctypes.data_as(C.POINTER(C.c_int32))
+    d.materials, d.textures, d.lights = mats, texs, lts
+    return d, (pos, nrm, uv, mat_id, mats, lts, texs, tex_keep)
+
+
+class Context:
+    """One GPU. Raises McptError if there is no usable B200 (no CPU fallback exists)."""
+
+    def __init__(self, device=0):
+        self._c = C.c_void_p()
+        check(lib().mcpt_create(int(device), C.byref(self._c)))
+        self.n_faces = 0
+        self.last_stats = capi.Stats()
+
+    def close(self):
+        if self._c:
+            lib().mcpt_destroy(self._c)
+            self._c = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream_ptr):
+        check(lib().mcpt_set_stream(self._c, C.c_void_p(cuda_stream_ptr)))
+
+    def set_seed(self, seed):
+        check(lib().mcpt_set_seed(self._c, C.c_uint64(seed)))
+
+    def upload_scene(self, desc):
+        """desc: HostScene, SceneDesc or pointer to one."""
+        if isinstance(desc, HostScene):
+            desc = desc.desc
+        check(lib().mcpt_upload_scene(self._c, C.byref(desc)))
+        self.n_faces = desc.n_faces
+
+    def build_bvh(self):
+        ms = C.c_float()
+        check(lib().mcpt_build_bvh(self._c, C.byref(ms)))
+        return ms.value
+
+    def get_morton(self):
+        n = self.n_faces
+        codes_obj, codes_sorted = np.empty(n, np.uint32), np.empty(n, np.uint32)
+        face_sorted = np.empty(n, np.int32)
+        check(lib().mcpt_get_morton(self._c, codes_obj.ctypes.data, codes_sorted.ctypes.data, face_sorted.ctypes.data))
+        return codes_obj, codes_sorted, face_sorted
+
+    def get_nodes(self):
+        nn = max(self.n_faces - 1, 1)
+        nodes = np.empty((nn, 16), np.float32)
+        root = C.c_int32()
+        check(lib().mcpt_get_nodes(self._c, nodes.ctypes.data, C.byref(root)))
+        return nodes, root.value
+
+    def trace(self, org_dir):
+        """org_dir: (n,6) float32 host array -> structured array of hits (t,u,v,tri,leaf)."""
+        rays = np.ascontiguousarray(org_dir, dtype=np.float32).reshape(-1, 6)
+        n = rays.shape[0]
+        hits = np.empty(n, dtype=np.dtype([("t", "f4"), ("u", "f4"), ("v", "f4"), ("tri", "i4"), ("leaf", "i4")]))
+        st = capi.Stats()
+        check(lib().mcpt_trace(self._c, rays.ctypes.data, n, hits.ctypes.data, C.byref(st)))
+        self.last_stats = st
+        return hits
+
+    def trace_device(self, d_org_dir_ptr, n, d_hits_ptr, flags=0):
+        st = capi.Stats()
+        check(lib().mcpt_trace_device(self._c, C.c_void_p(d_org_dir_ptr), n, C.c_void_p(d_hits_ptr), flags, C.byref(st)))
+        self.last_stats = st
+        return st
+
+    def render(self, camera, spp, width=0, height=0, mode=capi.MODE_MEGAKERNEL, flags=0, out=None):
+        """generateImg: mean radiance image (H,W,3) float32 in a HOST buffer."""
+        w = width if width > 0 else camera.width
+        h = height if height > 0 else camera.height
+        if out is None:
+            out = np.empty((h, w, 3), np.float32)
+        st = capi.Stats()
+        check(lib().mcpt_render(self._c, C.byref(camera), width, height, spp, mode, flags, out.ctypes.data, C.byref(st)))
+        self.last_stats = st
+        return out
+
+    def render_chunks(self, camera, spp, chunk_begin, chunk_end, d_partial_ptr, width=0, height=0,
+                      mode=capi.MODE_MEGAKERNEL, flags=0):
+        st = capi.Stats()
+        check(lib().mcpt_render_chunks(self._c, C.byref(camera), width, height, spp, chunk_begin, chunk_end, mode, flags,
+                                       C.c_void_p(d_partial_ptr), C.byref(st)))
+        self.last_stats = st
+        return st
+
+    def sum_partials(self, d_partials_ptr, n, count, scale, d_out_ptr):
+        check(lib().mcpt_sum_partials(self._c, C.c_void_p(d_partials_ptr), n, count, scale, C.c_void_p(d_out_ptr)))
+
+
+def render_scene(path, filename, spp, out_dir=None, device=0):
+    """render_scene(path, filename, spp) of MTPC/MTPC.cpp:35: writes <out_dir><filename>-SPP<spp>.png."""
+    check(lib().mcpt_render_scene(path.encode(), filename.encode(), int(spp), out_dir.encode() if out_dir else None, device))
+    return True
+
+
+def write_png(file, rgb):
+    a = np.ascontiguousarray(rgb, dtype=np.float32)
+    h, w = a.shape[0], a.shape[1]
+    check(lib().mcpt_write_png(file.encode(), a.ctypes.data_as(C.POINTER(C.c_float)), w, h))

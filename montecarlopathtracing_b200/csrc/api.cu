@@ -1,0 +1,429 @@
+// api.cu — the C ABI of include/mcpt.h (device side): context, scene upload, seams 1-3.
+// No CPU fallback: every entry point that computes needs a CUDA device with sm_100a code.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "lbvh.h"
+#include "render.h"
+
+void mcpt_set_error(const char* msg);  // host/mcpt_error.cpp
+
+using namespace mcpt;
+
+struct mcpt_ctx {
+    int device = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+    uint64_t seed = 0;
+    SceneBuffers sb;
+    DMaterial* d_materials = nullptr; DTexture* d_textures = nullptr; unsigned char* d_tex_bytes = nullptr;
+    DLight* d_lights = nullptr; LightTri* d_light_tris = nullptr; float* d_light_cdf = nullptr;
+    int n_materials = 0, n_textures = 0, n_lights = 0;
+    float area0 = 0.f;
+    unsigned long long* d_counters = nullptr;
+    float* d_planes = nullptr; size_t planes_cap = 0;   // scratch: sample-chunk planes
+    float* d_image = nullptr; size_t image_cap = 0;     // scratch: reduced image
+    void* d_io = nullptr; size_t io_cap = 0;            // scratch: rays in / hits out of mcpt_trace
+    float last_build_ms = 0.f;
+    bool scene_loaded = false;
+};
+
+namespace {
+int fail_cuda(cudaError_t e, const char* what) {
+    std::string m = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    mcpt_set_error(m.c_str());
+    return MCPT_ERR_CUDA;
+}
+int fail_arg(const char* what) { mcpt_set_error(what); return MCPT_ERR_ARG; }
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail_cuda(e_, #call); } while (0)
+
+template <class T> cudaError_t dev_alloc(T*& p, size_t count) {
+    if (p) { cudaFree(p); p = nullptr; }
+    return cudaMalloc((void**)&p, sizeof(T) * (count ? count : 1));
+}
+template <class T> cudaError_t grow(T*& p, size_t& cap, size_t bytes) {
+    if (bytes <= cap && p) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    cudaError_t e = cudaMalloc((void**)&p, bytes ? bytes : 1);
+    if (e == cudaSuccess) cap = bytes;
+    return e;
+}
+void free_scene(mcpt_ctx* c) {
+    SceneBuffers& s = c->sb;
+    cudaFree(s.pos); cudaFree(s.nrm); cudaFree(s.uv); cudaFree(s.mat_id); cudaFree(s.codes_obj); cudaFree(s.codes_sorted);
+    cudaFree(s.iota); cudaFree(s.leaf_face); cudaFree(s.leaf_parent); cudaFree(s.flags); cudaFree(s.nodes); cudaFree(s.tri);
+    cudaFree(s.shade); cudaFree(s.root_box); cudaFree(s.cub_temp);
+    s = SceneBuffers();
+    cudaFree(c->d_materials); cudaFree(c->d_textures); cudaFree(c->d_tex_bytes); cudaFree(c->d_lights);
+    cudaFree(c->d_light_tris); cudaFree(c->d_light_cdf);
+    c->d_materials = nullptr; c->d_textures = nullptr; c->d_tex_bytes = nullptr; c->d_lights = nullptr;
+    c->d_light_tris = nullptr; c->d_light_cdf = nullptr;
+    c->scene_loaded = false;
+}
+// Face::calAera, MTPC/sceneManagement.cpp:399-406 (law of cosines), in double like the reference
+double face_area(const double* p) {
+    auto len = [](double x, double y, double z) { return std::sqrt(x * x + y * y + z * z); };
+    const double a = len(p[3] - p[0], p[4] - p[1], p[5] - p[2]), b = len(p[6] - p[0], p[7] - p[1], p[8] - p[2]),
+                 c = len(p[6] - p[3], p[7] - p[4], p[8] - p[5]);
+    const double cos_c = (a * a + b * b - c * c) / (2 * a * b);
+    return a * b * std::sqrt(1 - cos_c * cos_c) / 2;
+}
+DeviceScene device_scene(const mcpt_ctx* c) {
+    DeviceScene d{};
+    d.n_faces = c->sb.n_faces; d.n_materials = c->n_materials; d.n_textures = c->n_textures; d.n_lights = c->n_lights;
+    d.root = 0; d.area0 = c->area0;
+    d.nodes = c->sb.nodes; d.tri = c->sb.tri; d.shade = c->sb.shade; d.leaf_face = c->sb.leaf_face;
+    d.materials = c->d_materials; d.textures = c->d_textures; d.tex_bytes = c->d_tex_bytes;
+    d.lights = c->d_lights; d.light_tris = c->d_light_tris; d.light_cdf = c->d_light_cdf;
+    return d;
+}
+}  // namespace
+
+extern "C" {
+
+MCPT_API int mcpt_create(int device, mcpt_ctx** out) {
+    if (!out) return fail_arg("mcpt_create: null out");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaGetDeviceCount (no CUDA device: this library has no CPU fallback)");
+    if (device < 0 || device >= n) return fail_arg("mcpt_create: device index out of range");
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        mcpt_set_error("mcpt_create: kernels are built for sm_100a (B200) only");
+        return MCPT_ERR_CUDA;
+    }
+    mcpt_ctx* c = new mcpt_ctx;
+    c->device = device;
+    CU(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    c->stream = c->own_stream;
+    CU(cudaEventCreate(&c->ev0)); CU(cudaEventCreate(&c->ev1)); CU(cudaEventCreate(&c->ev2));
+    CU(dev_alloc(c->d_counters, 4));
+    *out = c;
+    return MCPT_OK;
+}
+
+MCPT_API void mcpt_destroy(mcpt_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_scene(c);
+    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2);
+    cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+MCPT_API int mcpt_set_stream(mcpt_ctx* c, void* s) {
+    if (!c) return fail_arg("mcpt_set_stream: null ctx");
+    c->stream = s ? (cudaStream_t)s : c->own_stream;
+    return MCPT_OK;
+}
+MCPT_API int mcpt_set_seed(mcpt_ctx* c, uint64_t seed) {
+    if (!c) return fail_arg("mcpt_set_seed: null ctx");
+    c->seed = seed;
+    return MCPT_OK;
+}
+
+MCPT_API int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
+    if (!c || !d) return fail_arg("mcpt_upload_scene: null argument");
+    if (d->n_faces <= 0 || !d->pos || !d->nrm || !d->uv || !d->mat_id) return fail_arg("mcpt_upload_scene: empty scene");
+    if (d->n_materials <= 0 || !d->materials) return fail_arg("mcpt_upload_scene: no materials");
+    const int n = d->n_faces;
+    for (int i = 0; i < n; i++)
+        if (d->mat_id[i] < 0 || d->mat_id[i] >= d->n_materials) return fail_arg("mcpt_upload_scene: mat_id out of range");
+    for (int l = 0; l < d->n_lights; l++)
+        if (d->lights[l].mat_id < 0 || d->lights[l].mat_id >= d->n_materials) return fail_arg("mcpt_upload_scene: light mat_id out of range");
+    for (int m = 0; m < d->n_materials; m++)
+        if (d->materials[m].tex_id >= d->n_textures) return fail_arg("mcpt_upload_scene: tex_id out of range");
+    CU(cudaSetDevice(c->device));
+    free_scene(c);
+    SceneBuffers& s = c->sb;
+    s.n_faces = n;
+    const size_t N = (size_t)n;
+    CU(dev_alloc(s.pos, 9 * N)); CU(dev_alloc(s.nrm, 9 * N)); CU(dev_alloc(s.uv, 6 * N)); CU(dev_alloc(s.mat_id, N));
+    CU(dev_alloc(s.codes_obj, N)); CU(dev_alloc(s.codes_sorted, N)); CU(dev_alloc(s.iota, N)); CU(dev_alloc(s.leaf_face, N));
+    CU(dev_alloc(s.leaf_parent, N)); CU(dev_alloc(s.flags, N)); CU(dev_alloc(s.nodes, N)); CU(dev_alloc(s.tri, N));
+    CU(dev_alloc(s.shade, N)); CU(dev_alloc(s.root_box, 6));
+    s.cub_temp_bytes = lbvh_sort_temp_bytes(n);
+    CU(cudaMalloc(&s.cub_temp, s.cub_temp_bytes ? s.cub_temp_bytes : 1));
+    cudaStream_t st = c->stream;
+    CU(cudaMemcpyAsync(s.pos, d->pos, 72 * N, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s.nrm, d->nrm, 72 * N, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s.uv, d->uv, 48 * N, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(s.mat_id, d->mat_id, 4 * N, cudaMemcpyHostToDevice, st));
+
+    // materials: light_id = light_map lookup (the last "mtlname" line naming the material wins, sceneManagement.cpp:256)
+    std::vector<DMaterial> mats(d->n_materials);
+    for (int m = 0; m < d->n_materials; m++) {
+        const mcpt_material& src = d->materials[m];
+        DMaterial& t = mats[m];
+        for (int k = 0; k < 3; k++) { t.kd[k] = (float)src.kd[k]; t.ks[k] = (float)src.ks[k]; }
+        t.kd_norm = (float)std::sqrt(src.kd[0] * src.kd[0] + src.kd[1] * src.kd[1] + src.kd[2] * src.kd[2]);
+        t.ks_norm = (float)std::sqrt(src.ks[0] * src.ks[0] + src.ks[1] * src.ks[1] + src.ks[2] * src.ks[2]);
+        t.Ns = (float)src.Ns; t.Ni = (float)src.Ni; t.tex_id = src.tex_id; t.light_id = -1;
+    }
+    for (int l = 0; l < d->n_lights; l++) mats[d->lights[l].mat_id].light_id = l;
+    // textures, packed back to back
+    std::vector<DTexture> texs(d->n_textures);
+    std::vector<unsigned char> tex_bytes;
+    for (int i = 0; i < d->n_textures; i++) {
+        const mcpt_texture& t = d->textures[i];
+        if (t.height <= 0 || t.width <= 0 || !t.bgr) return fail_arg("mcpt_upload_scene: bad texture");
+        texs[i].height = t.height; texs[i].width = t.width; texs[i].offset = tex_bytes.size();
+        tex_bytes.insert(tex_bytes.end(), t.bgr, t.bgr + (size_t)t.height * t.width * 3);
+    }
+    // lights: area CDF over the light material's faces in OBJ order (MTPC/pathTracing.cpp:177-184), built once
+    std::vector<DLight> lights(d->n_lights);
+    std::vector<LightTri> ltris;
+    std::vector<float> cdf;
+    std::vector<double> areas(d->n_lights, 0.0);
+    for (int l = 0; l < d->n_lights; l++) {
+        DLight& L = lights[l];
+        L.mat_id = d->lights[l].mat_id; L.first = (int)ltris.size(); L.count = 0;
+        for (int k = 0; k < 3; k++) L.radiance[k] = (float)d->lights[l].radiance[k];
+        double total = 0;
+        for (int i = 0; i < n; i++) {
+            if (d->mat_id[i] != L.mat_id) continue;
+            const double* p = d->pos + 9 * (size_t)i; const double* q = d->nrm + 9 * (size_t)i;
+            total += face_area(p);
+            cdf.push_back((float)total);
+            LightTri t;
+            t.p0n0x = make_float4((float)p[0], (float)p[1], (float)p[2], (float)q[0]);
+            t.p1n0y = make_float4((float)p[3], (float)p[4], (float)p[5], (float)q[1]);
+            t.p2n0z = make_float4((float)p[6], (float)p[7], (float)p[8], (float)q[2]);
+            t.n1n2x = make_float4((float)q[3], (float)q[4], (float)q[5], (float)q[6]);
+            t.n2yz = make_float4((float)q[7], (float)q[8], 0.f, 0.f);
+            ltris.push_back(t);
+            L.count++;
+        }
+        areas[l] = total; L.area = (float)total;
+    }
+    c->area0 = d->n_lights > 0 ? (float)areas[0] : 0.f;
+    for (int l = 0; l < d->n_lights; l++) {   // entries reachable by rnd <= area0 (quirk Q6): bounds the binary search
+        DLight& L = lights[l];
+        int m = 0;
+        while (m < L.count && !(cdf[L.first + m] > c->area0)) m++;
+        L.n_search = m < L.count ? m + 1 : L.count;
+    }
+    c->n_materials = d->n_materials; c->n_textures = d->n_textures; c->n_lights = d->n_lights;
+    CU(dev_alloc(c->d_materials, mats.size())); CU(dev_alloc(c->d_textures, texs.size())); CU(dev_alloc(c->d_tex_bytes, tex_bytes.size()));
+    CU(dev_alloc(c->d_lights, lights.size())); CU(dev_alloc(c->d_light_tris, ltris.size())); CU(dev_alloc(c->d_light_cdf, cdf.size()));
+    CU(cudaMemcpyAsync(c->d_materials, mats.data(), sizeof(DMaterial) * mats.size(), cudaMemcpyHostToDevice, st));
+    if (!texs.empty()) CU(cudaMemcpyAsync(c->d_textures, texs.data(), sizeof(DTexture) * texs.size(), cudaMemcpyHostToDevice, st));
+    if (!tex_bytes.empty()) CU(cudaMemcpyAsync(c->d_tex_bytes, tex_bytes.data(), tex_bytes.size(), cudaMemcpyHostToDevice, st));
+    if (!lights.empty()) CU(cudaMemcpyAsync(c->d_lights, lights.data(), sizeof(DLight) * lights.size(), cudaMemcpyHostToDevice, st));
+    if (!ltris.empty()) CU(cudaMemcpyAsync(c->d_light_tris, ltris.data(), sizeof(LightTri) * ltris.size(), cudaMemcpyHostToDevice, st));
+    if (!cdf.empty()) CU(cudaMemcpyAsync(c->d_light_cdf, cdf.data(), sizeof(float) * cdf.size(), cudaMemcpyHostToDevice, st));
+    CU(cudaStreamSynchronize(st));  // the staging vectors die here
+    c->scene_loaded = true;
+    return MCPT_OK;
+}
+
+MCPT_API int mcpt_build_bvh(mcpt_ctx* c, float* ms_out) {
+    if (!c || !c->scene_loaded) return fail_arg("mcpt_build_bvh: upload a scene first");
+    CU(cudaSetDevice(c->device));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    int launches = 0;
+    const int e = lbvh_build(c->sb, c->stream, &launches);
+    if (e) return fail_cuda((cudaError_t)e, "lbvh_build");
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaEventSynchronize(c->ev1));
+    CU(cudaEventElapsedTime(&c->last_build_ms, c->ev0, c->ev1));
+    if (ms_out) *ms_out = c->last_build_ms;
+    return MCPT_OK;
+}
+
+MCPT_API int mcpt_get_morton(mcpt_ctx* c, uint32_t* codes_obj, uint32_t* codes_sorted, int32_t* face_sorted) {
+    if (!c || !c->sb.built) return fail_arg("mcpt_get_morton: build the BVH first");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    const size_t b = 4 * (size_t)c->sb.n_faces;
+    if (codes_obj) CU(cudaMemcpy(codes_obj, c->sb.codes_obj, b, cudaMemcpyDeviceToHost));
+    if (codes_sorted) CU(cudaMemcpy(codes_sorted, c->sb.codes_sorted, b, cudaMemcpyDeviceToHost));
+    if (face_sorted) CU(cudaMemcpy(face_sorted, c->sb.leaf_face, b, cudaMemcpyDeviceToHost));
+    return MCPT_OK;
+}
+
+MCPT_API int mcpt_get_nodes(mcpt_ctx* c, float* nodes16, int32_t* root) {
+    if (!c || !c->sb.built) return fail_arg("mcpt_get_nodes: build the BVH first");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    const int n_nodes = c->sb.n_faces > 1 ? c->sb.n_faces - 1 : 1;
+    if (nodes16) CU(cudaMemcpy(nodes16, c->sb.nodes, sizeof(BvhNode) * (size_t)n_nodes, cudaMemcpyDeviceToHost));
+    if (root) *root = 0;
+    return MCPT_OK;
+}
+
+namespace {
+void fill_stats(mcpt_ctx* c, mcpt_stats* st, double samples, const unsigned long long cnt[3], float ms, int launches) {
+    if (!st) return;
+    st->samples = samples; st->rays = (double)cnt[0]; st->node_visits = (double)cnt[1]; st->tri_tests = (double)cnt[2];
+    st->render_ms = ms; st->build_ms = c->last_build_ms; st->kernel_launches = launches; st->integrate_ms = 0.f;
+}
+// generateImg's camera basis (MTPC/pathTracing.cpp:276-294), in double on the host
+DCamera make_camera(const mcpt_camera* cam, int width, int height) {
+    DCamera d{};
+    const double PI = 3.1415926;  // MTPC/pathTracing.h:11
+    double up[3] = {cam->up[0], cam->up[1], cam->up[2]};
+    const double ul = std::sqrt(up[0] * up[0] + up[1] * up[1] + up[2] * up[2]);
+    for (double& v : up) v /= ul;
+    double dir[3];
+    for (int k = 0; k < 3; k++) dir[k] = cam->lookat[k] - cam->eye[k];
+    const double l = std::sqrt(dir[0] * dir[0] + dir[1] * dir[1] + dir[2] * dir[2]);
+    const double dy = std::tan(cam->fovy / 2 / 180 * PI) * l;
+    const double dx = dy / height * width;
+    const double pdx = 2 * dx / width, pdy = 2 * dy / height;
+    double X[3] = {dir[1] * up[2] - up[1] * dir[2], up[0] * dir[2] - dir[0] * up[2], dir[0] * up[1] - up[0] * dir[1]};
+    const double xl = std::sqrt(X[0] * X[0] + X[1] * X[1] + X[2] * X[2]);
+    for (double& v : X) v /= xl;
+    for (int k = 0; k < 3; k++) {
+        d.eye[k] = cam->eye[k];
+        d.start[k] = cam->lookat[k] - X[k] * dx + up[k] * dy;
+        d.pdx[k] = X[k] * pdx;
+        d.pdy[k] = up[k] * pdy;
+    }
+    d.width = width; d.height = height;
+    return d;
+}
+// Enqueue the integrator for chunks [cb, ce) into c->d_planes (ce-cb planes). No sync.
+int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, int spp, int cb, int ce, int mode, int flags,
+                   int* launches) {
+    if (mode != MCPT_MODE_MEGAKERNEL) return fail_arg("render: only MCPT_MODE_MEGAKERNEL is implemented in this build");
+    const int nch = ce - cb;
+    const size_t plane = (size_t)width * height * 3;
+    CU(grow(c->d_planes, c->planes_cap, sizeof(float) * plane * nch));
+    RenderParams P{};
+    P.scene = device_scene(c);
+    P.cam = make_camera(cam, width, height);
+    P.spp = spp; P.chunk_begin = cb; P.n_chunks = nch;
+    // enough threads to fill 148 SMs several times over, otherwise as many samples per thread as possible
+    int g = nch;
+    while (g > 1 && (long long)width * height * (nch / g) < 600000LL) g >>= 1;
+    P.chunks_per_thread = g;
+    P.seed_lo = (unsigned)c->seed; P.seed_hi = (unsigned)(c->seed >> 32);
+    P.planes = c->d_planes; P.counters = c->d_counters;
+    CU(cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), c->stream));
+    const int e = launch_megakernel(P, flags, c->stream);
+    if (e) return fail_cuda((cudaError_t)e, "pt_megakernel launch");
+    CU(cudaEventRecord(c->ev2, c->stream));
+    if (launches) *launches += 1;
+    return MCPT_OK;
+}
+int check_render_args(mcpt_ctx* c, const mcpt_camera* cam, int& width, int& height, int spp) {
+    if (!c || !cam) return fail_arg("render: null argument");
+    if (!c->sb.built) return fail_arg("render: build the BVH first");
+    if (width <= 0) width = cam->width;
+    if (height <= 0) height = cam->height;
+    if (width <= 0 || height <= 0 || spp <= 0) return fail_arg("render: width, height and spp must be positive");
+    return MCPT_OK;
+}
+}  // namespace
+
+MCPT_API int mcpt_trace_device(mcpt_ctx* c, const float* d_org_dir, int n, mcpt_hit* d_hits, int flags, mcpt_stats* st) {
+    if (!c || !c->sb.built) return fail_arg("mcpt_trace: build the BVH first");
+    if (n < 0 || (n > 0 && (!d_org_dir || !d_hits))) return fail_arg("mcpt_trace: bad buffers");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), c->stream));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    const int e = launch_trace(device_scene(c), d_org_dir, n, d_hits, (flags & MCPT_FLAG_COUNT) != 0, c->d_counters, c->stream);
+    if (e) return fail_cuda((cudaError_t)e, "trace_kernel launch");
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaEventSynchronize(c->ev1));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    unsigned long long cnt[4];
+    CU(cudaMemcpy(cnt, c->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
+    cnt[0] = (unsigned long long)n;
+    fill_stats(c, st, 0.0, cnt, ms, 1);
+    return MCPT_OK;
+}
+
+MCPT_API int mcpt_trace(mcpt_ctx* c, const float* org_dir, int n, mcpt_hit* hits_out, mcpt_stats* st) {
+    if (!c || !c->sb.built) return fail_arg("mcpt_trace: build the BVH first");
+    if (n < 0 || (n > 0 && (!org_dir || !hits_out))) return fail_arg("mcpt_trace: bad buffers");
+    if (n == 0) return MCPT_OK;
+    CU(cudaSetDevice(c->device));
+    const size_t in_b = 24 * (size_t)n, out_b = sizeof(mcpt_hit) * (size_t)n;
+    const size_t in_pad = (in_b + 255) & ~(size_t)255;
+    CU(grow(c->d_io, c->io_cap, in_pad + out_b));
+    float* d_in = (float*)c->d_io;
+    mcpt_hit* d_out = (mcpt_hit*)((char*)c->d_io + in_pad);
+    CU(cudaMemcpyAsync(d_in, org_dir, in_b, cudaMemcpyHostToDevice, c->stream));
+    const int rc = mcpt_trace_device(c, d_in, n, d_out, MCPT_FLAG_COUNT, st);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(hits_out, d_out, out_b, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return MCPT_OK;
+}
+
+MCPT_API int mcpt_sum_partials(mcpt_ctx* c, const float* d_partials, int n, int64_t count, float scale, float* d_out) {
+    if (!c || !d_partials || !d_out || count < 0) return fail_arg("mcpt_sum_partials: bad argument");
+    if (!(n == 1 || n == 2 || n == 4 || n == 8)) return fail_arg("mcpt_sum_partials: n must be 1, 2, 4 or 8");
+    CU(cudaSetDevice(c->device));
+    const int e = launch_sum_planes(d_partials, n, (long long)count, scale, d_out, c->stream);
+    if (e) return fail_cuda((cudaError_t)e, "sum_planes launch");
+    return MCPT_OK;
+}
+
+MCPT_API int mcpt_render_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, int spp, int cb, int ce, int mode,
+                                int flags, float* d_partial, mcpt_stats* st) {
+    int rc = check_render_args(c, cam, width, height, spp);
+    if (rc) return rc;
+    const int nch = ce - cb;
+    if (cb < 0 || ce > MCPT_NUM_CHUNKS || !(nch == 1 || nch == 2 || nch == 4 || nch == 8) || cb % nch != 0)
+        return fail_arg("mcpt_render_chunks: [chunk_begin, chunk_end) must be an aligned power-of-two range within 0..8");
+    if (!d_partial) return fail_arg("mcpt_render_chunks: null output");
+    CU(cudaSetDevice(c->device));
+    int launches = 0;
+    CU(cudaEventRecord(c->ev0, c->stream));
+    rc = enqueue_chunks(c, cam, width, height, spp, cb, ce, mode, flags, &launches);
+    if (rc) return rc;
+    const long long count = (long long)width * height * 3;
+    const int e = launch_sum_planes(c->d_planes, nch, count, 1.0f, d_partial, c->stream);
+    if (e) return fail_cuda((cudaError_t)e, "sum_planes launch");
+    launches++;
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaEventSynchronize(c->ev1));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    unsigned long long cnt[4];
+    CU(cudaMemcpy(cnt, c->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
+    const long long s0 = (long long)cb * spp / MCPT_NUM_CHUNKS, s1 = (long long)ce * spp / MCPT_NUM_CHUNKS;
+    fill_stats(c, st, (double)width * height * (double)(s1 - s0), cnt, ms, launches);
+    if (st) CU(cudaEventElapsedTime(&st->integrate_ms, c->ev0, c->ev2));
+    return MCPT_OK;
+}
+
+MCPT_API int mcpt_render(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, int spp, int mode, int flags, float* rgb_out,
+                         mcpt_stats* st) {
+    int rc = check_render_args(c, cam, width, height, spp);
+    if (rc) return rc;
+    if (!rgb_out) return fail_arg("mcpt_render: null output");
+    CU(cudaSetDevice(c->device));
+    const size_t count = (size_t)width * height * 3;
+    CU(grow(c->d_image, c->image_cap, sizeof(float) * count));
+    int launches = 0;
+    CU(cudaEventRecord(c->ev0, c->stream));
+    rc = enqueue_chunks(c, cam, width, height, spp, 0, MCPT_NUM_CHUNKS, mode, flags, &launches);
+    if (rc) return rc;
+    const int e = launch_sum_planes(c->d_planes, MCPT_NUM_CHUNKS, (long long)count, 1.0f / (float)spp, c->d_image, c->stream);
+    if (e) return fail_cuda((cudaError_t)e, "sum_planes launch");
+    launches++;
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaMemcpyAsync(rgb_out, c->d_image, sizeof(float) * count, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    unsigned long long cnt[4];
+    CU(cudaMemcpy(cnt, c->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
+    fill_stats(c, st, (double)width * height * (double)spp, cnt, ms, launches);
+    if (st) CU(cudaEventElapsedTime(&st->integrate_ms, c->ev0, c->ev2));
+    return MCPT_OK;
+}
+
+}  // extern "C"

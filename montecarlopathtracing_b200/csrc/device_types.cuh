@@ -1,0 +1,79 @@
+// Device-side data model shared by the build (lbvh.cu), traversal/integrator (render.cu) and the
+// C ABI (api.cu).  Everything the kernels touch lives in HBM in the layouts described in DESIGN.md.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/mcpt.h"
+
+namespace mcpt {
+
+// BVH node, 64 B = 4 x float4 (one 128-B line holds two nodes; every field is a 16-B vector load):
+//   q[0] = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)
+//   q[1] = (c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y)
+//   q[2] = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)
+//   q[3] = (child0, child1, parent, unused) as int bits; child >= 0: internal node, child < 0: leaf ~child
+struct __align__(16) BvhNode { float4 q[4]; };
+
+// Triangle, 48 B = 3 x float4, Morton-sorted leaf order: (v0, mat_id), (e1 = v1-v0, face_id), (e2 = v2-v0, 0)
+struct __align__(16) TriGeom { float4 v0m, e1f, e2; };
+
+// Shading attributes, 64 B = 4 x float4, same order:
+//   a = (n0.xyz, n1.x)  b = (n1.yz, n2.xy)  c = (n2.z, uv0.xy, uv1.x)  d = (uv1.y, uv2.xy, 0)
+struct __align__(16) TriShade { float4 a, b, c, d; };
+
+// Light-sampling record per light triangle in OBJ (= CDF) order, 80 B: positions and vertex normals.
+struct __align__(16) LightTri { float4 p0n0x, p1n0y, p2n0z, n1n2x, n2yz; };
+
+struct DMaterial {
+    float kd[3]; float kd_norm;
+    float ks[3]; float ks_norm;
+    float Ns, Ni;
+    int tex_id;   // < 0: none
+    int light_id; // < 0: not emissive (light_map lookup, MTPC/pathTracing.cpp:141)
+};
+struct DTexture { int height, width; unsigned long long offset; };  // offset into tex_bytes
+struct DLight {
+    float radiance[3];
+    float area;       // total area (pdf_light = 1/area, MTPC/pathTracing.cpp:218)
+    int mat_id;
+    int first;        // first entry in light_tris / light_cdf
+    int count;        // triangles of that material
+    int n_search;     // entries whose CDF can be selected by rnd in [0, area of light 0) (quirk Q6)
+};
+
+struct DeviceScene {
+    int n_faces;
+    int n_materials, n_textures, n_lights;
+    int root;                 // >= 0 internal node, < 0 leaf (single-triangle scene)
+    float area0;              // area of light 0: the frozen range of the selection uniform (quirk Q6)
+    const BvhNode* nodes;
+    const TriGeom* tri;
+    const TriShade* shade;
+    const int* leaf_face;     // sorted leaf -> OBJ face index
+    const DMaterial* materials;
+    const DTexture* textures;
+    const unsigned char* tex_bytes;
+    const DLight* lights;
+    const LightTri* light_tris;
+    const float* light_cdf;
+};
+
+// Pinhole camera of generateImg (MTPC/pathTracing.cpp:276-294), basis precomputed on the host in double.
+struct DCamera {
+    double eye[3], start[3], pdx[3], pdy[3];  // pixel (j,i) point = start - pdy*i + pdx*j
+    int width, height;
+};
+
+struct RenderParams {
+    DeviceScene scene;
+    DCamera cam;
+    int spp;            // total samples per pixel of the whole (multi-GPU) render
+    int chunk_begin;    // first sample chunk rendered by this launch
+    int n_chunks;       // chunks rendered by this launch
+    int chunks_per_thread;
+    unsigned seed_lo, seed_hi;
+    float* planes;      // n_chunks planes of height*width*3 floats: per-chunk SUM of sample radiance
+    unsigned long long* counters; // [0] rays, [1] node visits, [2] triangle tests
+};
+
+}  // namespace mcpt

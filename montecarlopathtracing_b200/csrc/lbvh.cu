@@ -1,0 +1,189 @@
+// lbvh.cu — seam 1 on the GPU: Morton codes -> radix sort -> Karras radix tree -> refit + layout.
+// Replaces getMortonCode (MTPC/morton code.cpp:3-32), the std::sort by code (MTPC/MTPC.cpp:44,
+// MTPC/sceneManagement.cpp:311-314) and the balanced-tree BVH (MTPC/BVH.cpp:44-132).
+// This file is compiled WITHOUT fused multiply-add (--fmad=false, see build.py): K1's float pipeline
+// must be IEEE-identical to the host's.
+#include <cub/device/device_radix_sort.cuh>
+#include "lbvh.h"
+
+namespace mcpt {
+
+// ---- K1: Morton codes --------------------------------------------------------------------------
+__device__ __forceinline__ unsigned expand_bits_10(unsigned v) {
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+// (x - MINP) / (MAXP - MINP) with the integer macros MINP=-1, MAXP=4 (MTPC/morton code.h:6-7):
+// float subtract, float divide by 5, then *1024, clamp to [0,1023], truncate.
+__device__ __forceinline__ unsigned quantize_axis(float x) {
+    float m = __fdiv_rn(__fsub_rn(x, -1.0f), 5.0f);
+    m = __fmul_rn(m, 1024.0f);
+    m = fminf(fmaxf(m, 0.0f), 1023.0f);
+    return (unsigned)m;
+}
+// One thread per face.  The centroid is formed in FP64 from the FP64 vertices and only then narrowed
+// to FP32, exactly like the call at MTPC/sceneManagement.cpp:176-179.
+__global__ void __launch_bounds__(256) morton_kernel(const double* __restrict__ pos, int n, uint32_t* __restrict__ codes,
+                                                     int* __restrict__ iota) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double* p = pos + 9 * (size_t)i;
+    const double cx = __ddiv_rn(__dadd_rn(__dadd_rn(p[0], p[3]), p[6]), 3.0);
+    const double cy = __ddiv_rn(__dadd_rn(__dadd_rn(p[1], p[4]), p[7]), 3.0);
+    const double cz = __ddiv_rn(__dadd_rn(__dadd_rn(p[2], p[5]), p[8]), 3.0);
+    const unsigned xx = expand_bits_10(quantize_axis(__double2float_rn(cx)));
+    const unsigned yy = expand_bits_10(quantize_axis(__double2float_rn(cy)));
+    const unsigned zz = expand_bits_10(quantize_axis(__double2float_rn(cz)));
+    codes[i] = xx * 4u + yy * 2u + zz;  // x is the most significant axis (morton code.cpp:20)
+    iota[i] = i;
+}
+
+// ---- K2: Karras 2012 radix tree over keys (code << 32 | sorted position) -------------------------
+__device__ __forceinline__ int delta(const uint32_t* __restrict__ codes, int n, int i, unsigned long long ki, int j) {
+    if (j < 0 || j >= n) return -1;
+    const unsigned long long kj = ((unsigned long long)codes[j] << 32) | (unsigned)j;
+    return __clzll((long long)(ki ^ kj));
+}
+__global__ void __launch_bounds__(256) radix_tree_kernel(const uint32_t* __restrict__ codes, int n, BvhNode* nodes,
+                                                         int* __restrict__ leaf_parent) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const unsigned long long ki = ((unsigned long long)codes[i] << 32) | (unsigned)i;
+    const int d = (delta(codes, n, i, ki, i + 1) - delta(codes, n, i, ki, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta(codes, n, i, ki, i - d);
+    int lmax = 2;
+    while (delta(codes, n, i, ki, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(codes, n, i, ki, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = delta(codes, n, i, ki, j);
+    int s = 0;
+    for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+        if (delta(codes, n, i, ki, i + (s + t) * d) > dnode) s += t;
+        if (t == 1) break;
+    }
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    const int c0 = (lo == gamma) ? ~gamma : gamma;
+    const int c1 = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    int* self = reinterpret_cast<int*>(&nodes[i].q[3]);
+    self[0] = c0; self[1] = c1; self[3] = 0;
+    if (i == 0) self[2] = -1;
+    if (c0 < 0) leaf_parent[gamma] = i; else reinterpret_cast<int*>(&nodes[c0].q[3])[2] = i;
+    if (c1 < 0) leaf_parent[gamma + 1] = i; else reinterpret_cast<int*>(&nodes[c1].q[3])[2] = i;
+}
+
+// ---- K3: leaf emit (traversal layout) + bottom-up AABB refit with atomic arrival counters ----------
+// One thread per sorted leaf: gathers the face's FP64 inputs once, writes the 48-B triangle and the
+// 64-B shading record, forms a conservatively padded FP32 box and carries it up the tree.  At each
+// parent the first child to arrive stores its box in the parent's slot and stops; the second one
+// reads the sibling's box back (L2, volatile) and continues with the union.
+struct Box3 { float lo[3], hi[3]; };
+
+__device__ __forceinline__ void store_child_box(BvhNode* node, int slot, const Box3& b) {
+    // q[slot] = (lo.x, hi.x, lo.y, hi.y); q[2].xy or .zw = (lo.z, hi.z).  .cg stores/loads: L2 is the
+    // point of coherence between the two sibling threads (they may sit on different SMs).
+    __stcg(&node->q[slot], make_float4(b.lo[0], b.hi[0], b.lo[1], b.hi[1]));
+    __stcg(reinterpret_cast<float2*>(&node->q[2]) + slot, make_float2(b.lo[2], b.hi[2]));
+}
+__device__ __forceinline__ Box3 load_child_box(const BvhNode* node, int slot) {
+    const float4 xy = __ldcg(&node->q[slot]);
+    const float2 z = __ldcg(reinterpret_cast<const float2*>(&node->q[2]) + slot);
+    Box3 b;
+    b.lo[0] = xy.x; b.hi[0] = xy.y; b.lo[1] = xy.z; b.hi[1] = xy.w; b.lo[2] = z.x; b.hi[2] = z.y;
+    return b;
+}
+
+__global__ void __launch_bounds__(256) emit_refit_kernel(int n, const double* __restrict__ pos, const double* __restrict__ nrm,
+                                                         const double* __restrict__ uv, const int* __restrict__ mat_id,
+                                                         const int* __restrict__ leaf_face, const int* __restrict__ leaf_parent,
+                                                         BvhNode* nodes, unsigned* flags, TriGeom* __restrict__ tri,
+                                                         TriShade* __restrict__ shade, float* __restrict__ root_box) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const int f = leaf_face[k];
+    const double* p = pos + 9 * (size_t)f;
+    float v[9];
+#pragma unroll
+    for (int a = 0; a < 9; a++) v[a] = __double2float_rn(p[a]);
+    TriGeom g;
+    g.v0m = make_float4(v[0], v[1], v[2], __int_as_float(mat_id[f]));
+    g.e1f = make_float4(v[3] - v[0], v[4] - v[1], v[5] - v[2], __int_as_float(f));
+    g.e2 = make_float4(v[6] - v[0], v[7] - v[1], v[8] - v[2], 0.0f);
+    tri[k] = g;
+    const double* q = nrm + 9 * (size_t)f;
+    const double* t = uv + 6 * (size_t)f;
+    TriShade s;
+    s.a = make_float4((float)q[0], (float)q[1], (float)q[2], (float)q[3]);
+    s.b = make_float4((float)q[4], (float)q[5], (float)q[6], (float)q[7]);
+    s.c = make_float4((float)q[8], (float)t[0], (float)t[1], (float)t[2]);
+    s.d = make_float4((float)t[3], (float)t[4], (float)t[5], 0.0f);
+    shade[k] = s;
+
+    Box3 b;
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        const float lo = fminf(fminf(v[a], v[3 + a]), v[6 + a]), hi = fmaxf(fmaxf(v[a], v[3 + a]), v[6 + a]);
+        const float pad = 4.0e-7f * fmaxf(fabsf(lo), fabsf(hi)) + 1.0e-30f;  // > 3 ulp: covers v0+e1 rounding and slab rounding
+        b.lo[a] = lo - pad; b.hi[a] = hi + pad;
+    }
+    if (n == 1) {  // degenerate tree: node 0 points at the only leaf twice
+        store_child_box(&nodes[0], 0, b); store_child_box(&nodes[0], 1, b);
+        int* c = reinterpret_cast<int*>(&nodes[0].q[3]);
+        c[0] = ~0; c[1] = ~0; c[2] = -1; c[3] = 0;
+        for (int a = 0; a < 3; a++) { root_box[a] = b.lo[a]; root_box[3 + a] = b.hi[a]; }
+        return;
+    }
+    int child = ~k;
+    int parent = leaf_parent[k];
+    while (true) {
+        BvhNode* node = &nodes[parent];
+        const int* c = reinterpret_cast<const int*>(&node->q[3]);
+        const int slot = (c[0] == child) ? 0 : 1;
+        store_child_box(node, slot, b);
+        __threadfence();
+        if (atomicAdd(&flags[parent], 1u) == 0u) return;  // sibling subtree not finished yet
+        const Box3 o = load_child_box(node, slot ^ 1);
+#pragma unroll
+        for (int a = 0; a < 3; a++) { b.lo[a] = fminf(b.lo[a], o.lo[a]); b.hi[a] = fmaxf(b.hi[a], o.hi[a]); }
+        child = parent;
+        parent = c[2];
+        if (parent < 0) break;
+    }
+    for (int a = 0; a < 3; a++) { root_box[a] = b.lo[a]; root_box[3 + a] = b.hi[a]; }
+}
+
+// ---- host-side orchestration -----------------------------------------------------------------------
+size_t lbvh_sort_temp_bytes(int n) {
+    size_t bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const int*)nullptr,
+                                    (int*)nullptr, n, 0, 30);
+    return bytes;
+}
+
+int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches) {
+    const int n = sb.n_faces;
+    const int tpb = 256;
+    int nl = 0;
+    morton_kernel<<<(n + tpb - 1) / tpb, tpb, 0, stream>>>(sb.pos, n, sb.codes_obj, sb.iota); nl++;
+    // stable LSD radix sort of (code, face index), 30 key bits: ties keep face-index order
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(sb.cub_temp, sb.cub_temp_bytes, sb.codes_obj, sb.codes_sorted, sb.iota,
+                                                    sb.leaf_face, n, 0, 30, stream);
+    if (e != cudaSuccess) return (int)e;
+    nl += 4;
+    if (n > 1) {
+        cudaMemsetAsync(sb.flags, 0, sizeof(unsigned) * (size_t)(n - 1), stream);
+        radix_tree_kernel<<<(n - 1 + tpb - 1) / tpb, tpb, 0, stream>>>(sb.codes_sorted, n, sb.nodes, sb.leaf_parent); nl++;
+    }
+    emit_refit_kernel<<<(n + tpb - 1) / tpb, tpb, 0, stream>>>(n, sb.pos, sb.nrm, sb.uv, sb.mat_id, sb.leaf_face, sb.leaf_parent,
+                                                               sb.nodes, sb.flags, sb.tri, sb.shade, sb.root_box); nl++;
+    if (launches) *launches = nl;
+    sb.built = true;
+    return (int)cudaGetLastError();
+}
+
+}  // namespace mcpt

@@ -1,0 +1,32 @@
+// GPU LBVH build (seam 1): buffers owned by a context and the build entry point.
+#pragma once
+#include "device_types.cuh"
+
+namespace mcpt {
+
+struct SceneBuffers {
+    int n_faces = 0;
+    // uploaded inputs, OBJ order (mcpt_scene_desc)
+    double* pos = nullptr; double* nrm = nullptr; double* uv = nullptr; int* mat_id = nullptr;
+    // build products
+    uint32_t* codes_obj = nullptr;     // Morton code of face i
+    uint32_t* codes_sorted = nullptr;  // ascending
+    int* iota = nullptr;               // 0..n-1 (sort values in)
+    int* leaf_face = nullptr;          // sorted leaf k -> OBJ face index
+    int* leaf_parent = nullptr;
+    unsigned* flags = nullptr;         // refit arrival counters, one per internal node
+    BvhNode* nodes = nullptr;          // max(n-1,1) internal nodes; root = node 0
+    TriGeom* tri = nullptr;            // sorted order
+    TriShade* shade = nullptr;         // sorted order
+    float* root_box = nullptr;         // 6 floats: lo.xyz, hi.xyz
+    void* cub_temp = nullptr; size_t cub_temp_bytes = 0;
+    bool built = false;
+};
+
+// Bytes of CUB temp storage needed for n faces.
+size_t lbvh_sort_temp_bytes(int n);
+// K1 Morton -> CUB radix sort -> K2 radix tree -> K3 leaf emit + atomic bottom-up refit.
+// Returns a cudaError_t as int; all work is enqueued on `stream`.
+int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches);
+
+}  // namespace mcpt

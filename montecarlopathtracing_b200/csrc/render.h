@@ -1,0 +1,13 @@
+// Launchers of the traversal / integrator / reduction kernels (render.cu).
+#pragma once
+#include "device_types.cuh"
+
+namespace mcpt {
+// K5: closest hit for n rays (org_dir = n x 6 floats, device). hits = n x mcpt_hit (device).
+int launch_trace(const DeviceScene& sc, const float* d_org_dir, int n, mcpt_hit* d_hits, bool count,
+                 unsigned long long* d_counters, cudaStream_t stream);
+// K6: megakernel integrator; fills P.planes (P.n_chunks planes).
+int launch_megakernel(const RenderParams& P, int flags, cudaStream_t stream);
+// K12: out[i] = scale * fixed pairwise tree sum over n planes (n in {1,2,4,8}).
+int launch_sum_planes(const float* d_planes, int n, long long count, float scale, float* d_out, cudaStream_t stream);
+}  // namespace mcpt

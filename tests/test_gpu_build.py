@@ -1,0 +1,112 @@
+"""GPU: seam 1 (Morton -> sort -> LBVH) through the C ABI, against the oracle and the reference's golden vectors."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+from scene_util import random_soup
+
+pytestmark = pytest.mark.gpu
+SCENE_NAMES = ("cornell-box", "veach-mis")
+
+
+@pytest.mark.parametrize("name", SCENE_NAMES)
+def test_morton_codes_and_leaf_order_bit_exact(gpu_ctx, scenes, name):
+    g = np.load(os.path.join(GOLDEN, name + "_morton.npz"))
+    gpu_ctx.upload_scene(scenes[name])
+    ms = gpu_ctx.build_bvh()
+    codes_obj, codes_sorted, face_sorted = gpu_ctx.get_morton()
+    assert np.array_equal(codes_obj, g["codes"])                       # every code, bit for bit, vs the reference
+    assert np.array_equal(face_sorted, g["perm"])                      # canonical leaf order (ties by face index)
+    assert np.array_equal(codes_sorted, g["codes"][g["perm"]])
+    assert ms > 0
+
+
+def check_tree(nodes, n, codes_sorted, tri_lo, tri_hi):
+    """Structural invariants of the radix tree + refit: every leaf reachable exactly once, leaf ranges contiguous and
+    nested, child boxes contain their subtree's triangles, parents recorded."""
+    child = nodes[:, 12:14].view(np.int32)
+    parent = nodes[:, 14].view(np.int32)
+    assert parent[0] == -1
+    seen = np.zeros(n, np.int32)
+    # iterative post-order: returns (lo_leaf, hi_leaf, box_lo, box_hi) per subtree
+    def box_of(i, slot):
+        q = nodes[i]
+        return np.array([q[4 * slot + 0], q[4 * slot + 2], q[8 + 2 * slot]]), np.array([q[4 * slot + 1], q[4 * slot + 3], q[9 + 2 * slot]])
+    result = {}
+    stack = [(0, False)]
+    while stack:
+        i, done = stack.pop()
+        if not done:
+            stack.append((i, True))
+            for c in child[i]:
+                if c >= 0:
+                    assert parent[c] == i
+                    stack.append((int(c), False))
+            continue
+        rng, lo_all, hi_all = [], np.full(3, np.inf), np.full(3, -np.inf)
+        for slot, c in enumerate(child[i]):
+            blo, bhi = box_of(i, slot)
+            if c < 0:
+                k = ~int(c); seen[k] += 1
+                lo, hi, klo, khi = tri_lo[k], tri_hi[k], k, k
+            else:
+                klo, khi, lo, hi = result.pop(int(c))
+            assert np.all(blo <= lo) and np.all(bhi >= hi), "child box does not contain its subtree"
+            assert np.all(blo >= lo - 1e-5 * (1 + np.abs(lo))) and np.all(bhi <= hi + 1e-5 * (1 + np.abs(hi))), "box not tight"
+            rng.append((klo, khi)); lo_all = np.minimum(lo_all, lo); hi_all = np.maximum(hi_all, hi)
+        assert rng[0][1] + 1 == rng[1][0], "children must cover adjacent leaf ranges"
+        result[i] = (rng[0][0], rng[1][1], lo_all, hi_all)
+    assert np.all(seen == 1)
+    lo, hi, _, _ = result[0]
+    assert (lo, hi) == (0, n - 1)
+
+
+@pytest.mark.parametrize("name", SCENE_NAMES)
+def test_tree_invariants_on_shipped_scenes(gpu_ctx, scenes, name):
+    s = scenes[name]
+    gpu_ctx.upload_scene(s)
+    gpu_ctx.build_bvh()
+    _, codes_sorted, face_sorted = gpu_ctx.get_morton()
+    nodes, root = gpu_ctx.get_nodes()
+    assert root == 0 and nodes.shape == (s.n_faces - 1, 16)
+    p = s.pos[face_sorted].astype(np.float32).astype(np.float64)
+    check_tree(nodes, s.n_faces, codes_sorted, p.min(axis=1), p.max(axis=1))
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 7, 64, 1001])
+def test_small_and_odd_triangle_counts(gpu_ctx, oracle, n):
+    """Edge cases the reference cannot even run (odd counts over-read, MTPC/BVH.cpp Q1): 1 triangle, odd counts,
+    many equal codes (all centroids clamp to the same cell when far outside [-1,4]^3)."""
+    desc, keep = random_soup(n, seed=n, far_outside=(n == 64))
+    gpu_ctx.upload_scene(desc)
+    gpu_ctx.build_bvh()
+    codes_obj, codes_sorted, face_sorted = gpu_ctx.get_morton()
+    want = oracle.morton(keep[0])
+    assert np.array_equal(codes_obj, want)
+    assert np.array_equal(face_sorted, oracle.stable_order(want))
+    if n == 64:
+        assert len(np.unique(codes_obj)) == 1
+    if n > 1:
+        nodes, _ = gpu_ctx.get_nodes()
+        p = keep[0].reshape(n, 3, 3)[face_sorted].astype(np.float32).astype(np.float64)
+        check_tree(nodes, n, codes_sorted, p.min(axis=1), p.max(axis=1))
+
+
+def test_large_mesh_sorted_and_idempotent(gpu_ctx, oracle):
+    """Size-independent properties at 1M triangles: keys sorted, permutation valid, rebuild gives the same order."""
+    n = 1 << 20
+    desc, keep = random_soup(n, seed=5, extent=2.4)
+    gpu_ctx.upload_scene(desc)
+    gpu_ctx.build_bvh()
+    c1, s1, f1 = gpu_ctx.get_morton()
+    assert np.all(np.diff(s1.astype(np.int64)) >= 0)
+    assert np.array_equal(np.sort(f1), np.arange(n))
+    assert np.array_equal(c1[f1], s1)
+    ties = np.diff(s1.astype(np.int64)) == 0
+    assert np.all(np.diff(f1)[ties] > 0)                   # equal codes keep face-index order
+    assert np.array_equal(c1, oracle.morton(keep[0]))      # all 1M codes bit-exact vs the CPU restatement
+    gpu_ctx.build_bvh()
+    c2, s2, f2 = gpu_ctx.get_morton()
+    assert np.array_equal(f1, f2) and np.array_equal(s1, s2)
