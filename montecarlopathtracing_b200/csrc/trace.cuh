@@ -18,6 +18,11 @@ namespace mcpt {
 struct Hit { float t, u, v; int k; };  // k = sorted-leaf index, -1 = miss
 
 #define MCPT_STACK_SIZE 64
+// Edge tolerance of the FP32 barycentric test.  The reference's FP64 same-side test is inclusive (>= 0), so a ray
+// through a shared edge hits one of the two triangles; in FP32 the rounding of u, v can put it just outside BOTH
+// (a crack: the image diagonals of cornell-box run exactly along wall edges).  Accepting |excess| <= 2e-6 closes the
+// cracks; which of two edge-sharing triangles wins is then decided by t like in the reference.
+#define MCPT_EDGE_EPS 2.0e-6f
 
 template <bool COUNT>
 __device__ __forceinline__ Hit trace_closest(const DeviceScene& sc, const float3 o, const float3 d, const float tmax,
@@ -75,7 +80,7 @@ __device__ __forceinline__ Hit trace_closest(const DeviceScene& sc, const float3
             const float3 qvec = cross(tvec, E1);
             const float v = dot(d, qvec) * inv_det;
             const float t = dot(E2, qvec) * inv_det;
-            if (u >= 0.0f && v >= 0.0f && u + v <= 1.0f && t > 0.0f && (t < best.t || (t == best.t && k < best.k))) {
+            if (u >= -MCPT_EDGE_EPS && v >= -MCPT_EDGE_EPS && u + v <= 1.0f + MCPT_EDGE_EPS && t > 0.0f && (t < best.t || (t == best.t && k < best.k))) {
                 best.t = t; best.u = u; best.v = v; best.k = k;
             }
         }
