@@ -236,7 +236,7 @@ def run_ours(args):
             "lbvh_build_ms": sum(build_ms) / len(build_ms), "render_ms": sum(render_ms) / len(render_ms),
             "e2e": {"value": samples / e2e_ms * 1e-3, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": h * w * 3 * 4, "ms_per_step": e2e_ms / args.steps},
-            "gpu_launches": (7 + 2) * args.steps,
+            "gpu_launches": (7 + 3 + (1 if world > 1 else 1)) * args.steps,   # build 7 (3 ours + 4 CUB), raygen, integrator, chunk sum, final sum
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
                          "traffic": None, "peak_source": pk_src, "kernel": "pt_megakernel", "kernel_ms": k_ms,

@@ -15,7 +15,7 @@ using namespace mcpt;
 struct mcpt_ctx {
     int device = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;  // ev3..ev2 bracket the integrator kernel
     uint64_t seed = 0;
     SceneBuffers sb;
     DMaterial* d_materials = nullptr; DTexture* d_textures = nullptr; unsigned char* d_tex_bytes = nullptr;
@@ -25,6 +25,9 @@ struct mcpt_ctx {
     unsigned long long* d_counters = nullptr;
     float* d_planes = nullptr; size_t planes_cap = 0;   // scratch: sample-chunk planes
     float* d_image = nullptr; size_t image_cap = 0;     // scratch: reduced image
+    float* d_dirs = nullptr; size_t dirs_cap = 0;       // scratch: primary ray directions (K7)
+    char* d_wf = nullptr; size_t wf_cap = 0;            // scratch: wavefront slot state + ray queue
+    unsigned* h_alive = nullptr;                        // pinned: live-slot count read back by the wavefront loop
     void* d_io = nullptr; size_t io_cap = 0;            // scratch: rays in / hits out of mcpt_trace
     float last_build_ms = 0.f;
     bool scene_loaded = false;
@@ -75,7 +78,7 @@ DeviceScene device_scene(const mcpt_ctx* c) {
     DeviceScene d{};
     d.n_faces = c->sb.n_faces; d.n_materials = c->n_materials; d.n_textures = c->n_textures; d.n_lights = c->n_lights;
     d.root = 0; d.area0 = c->area0;
-    d.nodes = c->sb.nodes; d.tri = c->sb.tri; d.shade = c->sb.shade; d.leaf_face = c->sb.leaf_face;
+    d.nodes = c->sb.nodes; d.tri = c->sb.tri; d.shade = c->sb.shade; d.leaf_face = c->sb.leaf_face; d.pos = c->sb.pos;
     d.materials = c->d_materials; d.textures = c->d_textures; d.tex_bytes = c->d_tex_bytes;
     d.lights = c->d_lights; d.light_tris = c->d_light_tris; d.light_cdf = c->d_light_cdf;
     return d;
@@ -101,8 +104,9 @@ MCPT_API int mcpt_create(int device, mcpt_ctx** out) {
     c->device = device;
     CU(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     c->stream = c->own_stream;
-    CU(cudaEventCreate(&c->ev0)); CU(cudaEventCreate(&c->ev1)); CU(cudaEventCreate(&c->ev2));
+    CU(cudaEventCreate(&c->ev0)); CU(cudaEventCreate(&c->ev1)); CU(cudaEventCreate(&c->ev2)); CU(cudaEventCreate(&c->ev3));
     CU(dev_alloc(c->d_counters, 4));
+    CU(cudaHostAlloc((void**)&c->h_alive, sizeof(unsigned), cudaHostAllocDefault));
     *out = c;
     return MCPT_OK;
 }
@@ -112,8 +116,8 @@ MCPT_API void mcpt_destroy(mcpt_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     free_scene(c);
-    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io);
-    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2);
+    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); cudaFreeHost(c->h_alive);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -293,13 +297,18 @@ DCamera make_camera(const mcpt_camera* cam, int width, int height) {
 // Enqueue the integrator for chunks [cb, ce) into c->d_planes (ce-cb planes). No sync.
 int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, int spp, int cb, int ce, int mode, int flags,
                    int* launches) {
-    if (mode != MCPT_MODE_MEGAKERNEL) return fail_arg("render: only MCPT_MODE_MEGAKERNEL is implemented in this build");
+    if (mode != MCPT_MODE_MEGAKERNEL && mode != MCPT_MODE_WAVEFRONT) return fail_arg("render: unknown mode");
     const int nch = ce - cb;
     const size_t plane = (size_t)width * height * 3;
     CU(grow(c->d_planes, c->planes_cap, sizeof(float) * plane * nch));
+    CU(grow(c->d_dirs, c->dirs_cap, sizeof(float) * plane));
     RenderParams P{};
     P.scene = device_scene(c);
     P.cam = make_camera(cam, width, height);
+    P.cam_dirs = c->d_dirs;
+    const int er = launch_raygen(P.cam, c->d_dirs, c->stream);
+    if (er) return fail_cuda((cudaError_t)er, "raygen_kernel launch");
+    if (launches) *launches += 1;
     P.spp = spp; P.chunk_begin = cb; P.n_chunks = nch;
     // enough threads to fill 148 SMs several times over, otherwise as many samples per thread as possible
     int g = nch;
@@ -308,10 +317,20 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
     P.seed_lo = (unsigned)c->seed; P.seed_hi = (unsigned)(c->seed >> 32);
     P.planes = c->d_planes; P.counters = c->d_counters;
     CU(cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), c->stream));
-    const int e = launch_megakernel(P, flags, c->stream);
-    if (e) return fail_cuda((cudaError_t)e, "pt_megakernel launch");
+    CU(cudaEventRecord(c->ev3, c->stream));
+    if (mode == MCPT_MODE_WAVEFRONT) {
+        const int n_slots = wavefront_slots(P);
+        if (n_slots < 0) return fail_arg("render: image too large for one wavefront pass (more than 2^26 path slots)");
+        if (c->n_lights > 32) return fail_arg("render: wavefront mode supports at most 32 lights");
+        CU(grow(c->d_wf, c->wf_cap, wavefront_scratch_bytes(n_slots, c->n_lights)));
+        const int e = launch_wavefront(P, flags, c->d_wf, c->h_alive, c->stream, launches);
+        if (e) return fail_cuda((cudaError_t)e, "wavefront loop");
+    } else {
+        const int e = launch_megakernel(P, flags, c->stream);
+        if (e) return fail_cuda((cudaError_t)e, "pt_megakernel launch");
+        if (launches) *launches += 1;
+    }
     CU(cudaEventRecord(c->ev2, c->stream));
-    if (launches) *launches += 1;
     return MCPT_OK;
 }
 int check_render_args(mcpt_ctx* c, const mcpt_camera* cam, int& width, int& height, int spp) {
@@ -395,7 +414,7 @@ MCPT_API int mcpt_render_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, 
     CU(cudaMemcpy(cnt, c->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
     const long long s0 = (long long)cb * spp / MCPT_NUM_CHUNKS, s1 = (long long)ce * spp / MCPT_NUM_CHUNKS;
     fill_stats(c, st, (double)width * height * (double)(s1 - s0), cnt, ms, launches);
-    if (st) CU(cudaEventElapsedTime(&st->integrate_ms, c->ev0, c->ev2));
+    if (st) CU(cudaEventElapsedTime(&st->integrate_ms, c->ev3, c->ev2));
     return MCPT_OK;
 }
 
@@ -422,7 +441,7 @@ MCPT_API int mcpt_render(mcpt_ctx* c, const mcpt_camera* cam, int width, int hei
     unsigned long long cnt[4];
     CU(cudaMemcpy(cnt, c->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
     fill_stats(c, st, (double)width * height * (double)spp, cnt, ms, launches);
-    if (st) CU(cudaEventElapsedTime(&st->integrate_ms, c->ev0, c->ev2));
+    if (st) CU(cudaEventElapsedTime(&st->integrate_ms, c->ev3, c->ev2));
     return MCPT_OK;
 }
 

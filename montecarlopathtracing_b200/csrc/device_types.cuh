@@ -50,6 +50,7 @@ struct DeviceScene {
     const TriGeom* tri;
     const TriShade* shade;
     const int* leaf_face;     // sorted leaf -> OBJ face index
+    const double* pos;        // FP64 vertex positions, OBJ order (9 per face): final-hit refinement of seam 2
     const DMaterial* materials;
     const DTexture* textures;
     const unsigned char* tex_bytes;
@@ -72,6 +73,7 @@ struct RenderParams {
     int n_chunks;       // chunks rendered by this launch
     int chunks_per_thread;
     unsigned seed_lo, seed_hi;
+    const float* cam_dirs; // height*width*3: primary ray directions from raygen_kernel (K7)
     float* planes;      // n_chunks planes of height*width*3 floats: per-chunk SUM of sample radiance
     unsigned long long* counters; // [0] rays, [1] node visits, [2] triangle tests
 };

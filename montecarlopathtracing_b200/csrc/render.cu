@@ -6,135 +6,36 @@
 // centroid-biased light points (Q7), the double receiver cosine and max(1,d) clamp (Q8), lobe
 // pick without pdf division (Q9).
 #include "render.h"
-#include "philox.cuh"
-#include "trace.cuh"
+#include "shade.cuh"
 
 namespace mcpt {
 
-#define MCPT_PI 3.1415926f       /* MTPC/pathTracing.h:11 */
-#define MCPT_P_RR 0.6f           /* MTPC/pathTracing.cpp:237 */
-#define MCPT_MAX_DEPTH 64        /* reference recursion is unbounded; 0.6^64 ~ 6e-15 (same cap as the oracle) */
-enum { LOBE_DIFFUSE = 0, LOBE_SPECULAR = 1, LOBE_TRANSMISSION = 2 };
-
-struct PathVertex { float3 p, pn, kd, wo; int mat; };
-
-// Hit -> shading point: position and barycentric normal (MTPC/pathTracing.cpp:345-351, not normalised),
-// material, kd or texel (MTPC/pathTracing.cpp:148-163).
-__device__ __forceinline__ void make_vertex(const DeviceScene& sc, const Hit& h, const float3 ray_d, PathVertex& vx) {
-    const TriGeom* g = &sc.tri[h.k];
-    const float4 v0 = __ldg(&g->v0m), e1 = __ldg(&g->e1f), e2 = __ldg(&g->e2);
-    const TriShade* s = &sc.shade[h.k];
-    const float4 sa = __ldg(&s->a), sb = __ldg(&s->b), sc4 = __ldg(&s->c), sd = __ldg(&s->d);
-    const float w = 1.0f - h.u - h.v;
-    vx.p = f3(v0) + f3(e1) * h.u + f3(e2) * h.v;
-    vx.pn = f3(sa.x, sa.y, sa.z) * w + f3(sa.w, sb.x, sb.y) * h.u + f3(sb.z, sb.w, sc4.x) * h.v;
-    vx.wo = -ray_d;
-    vx.mat = __float_as_int(v0.w);
-    const DMaterial* m = &sc.materials[vx.mat];
-    if (m->tex_id >= 0) {
-        const DTexture tx = sc.textures[m->tex_id];
-        const float row = sc4.y * w + sc4.w * h.u + sd.y * h.v;   // vt.x -> row (quirk Q5)
-        const float col = sc4.z * w + sd.x * h.u + sd.z * h.v;    // vt.y -> column
-        const float irow = row - floorf(row), icol = col - floorf(col);
-        const int r = min((int)(irow * tx.height), tx.height - 1), c = min((int)(icol * tx.width), tx.width - 1);
-        const unsigned char* px = sc.tex_bytes + tx.offset + ((size_t)r * tx.width + c) * 3;
-        vx.kd = f3(px[2] * (1.0f / 255.0f), px[1] * (1.0f / 255.0f), px[0] * (1.0f / 255.0f));  // BGR -> RGB
-    } else {
-        vx.kd = f3(m->kd[0], m->kd[1], m->kd[2]);
+// ---- K7: primary rays --------------------------------------------------------------------------------
+// generateImg walks a row by REPEATED ADDITION: pos = start - pdy*i, then pos += pdx per pixel
+// (MTPC/pathTracing.cpp:297,326).  The rounding of that walk is visible: on the centre column of an even-width image
+// start.x + j*pdx.x is exactly 0 when formed by one multiplication, which by quirk Q2 (d.x == 0 hits nothing) would
+// paint a black column the reference does not have.  One thread per row repeats the walk in FP64 with explicitly
+// rounded operations (no FMA contraction) and stores normalize(pos - eye) narrowed to FP32.
+__global__ void __launch_bounds__(32) raygen_kernel(const DCamera cam, float* __restrict__ dirs) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cam.height) return;
+    double px = __dsub_rn(cam.start[0], __dmul_rn(cam.pdy[0], (double)i));
+    double py = __dsub_rn(cam.start[1], __dmul_rn(cam.pdy[1], (double)i));
+    double pz = __dsub_rn(cam.start[2], __dmul_rn(cam.pdy[2], (double)i));
+    float* out = dirs + 3 * (size_t)i * cam.width;
+    for (int j = 0; j < cam.width; j++) {
+        const double dx = __dsub_rn(px, cam.eye[0]), dy = __dsub_rn(py, cam.eye[1]), dz = __dsub_rn(pz, cam.eye[2]);
+        const double l = sqrt(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
+        out[3 * j + 0] = (float)__ddiv_rn(dx, l);
+        out[3 * j + 1] = (float)__ddiv_rn(dy, l);
+        out[3 * j + 2] = (float)__ddiv_rn(dz, l);
+        px = __dadd_rn(px, cam.pdx[0]); py = __dadd_rn(py, cam.pdx[1]); pz = __dadd_rn(pz, cam.pdx[2]);
     }
 }
 
-// One light's next-event estimate (MTPC/pathTracing.cpp:171-231).  Returns false when nothing can be
-// added (no triangle selected, receiver faces away, zero weight) so the shadow ray is not traced.
-// contrib = kd/pi * Le * |w.vn|/|vn| * |w.pn|/|pn| * A / max(1,d)^2 * (w.pn); the caller multiplies by V.
-__device__ __forceinline__ bool sample_light(const DeviceScene& sc, const DLight& L, const PathVertex& vx, const float4 u,
-                                             float3& ray_o, float3& ray_d, float& ray_tmax, float3& contrib) {
-    const float rnd = u.x * sc.area0;  // quirk Q6
-    const float* cdf = sc.light_cdf + L.first;
-    int lo = 0, hi = L.n_search;      // first j with rnd < cdf[j]
-    while (lo < hi) { const int mid = (lo + hi) >> 1; if (rnd < __ldg(&cdf[mid])) hi = mid; else lo = mid + 1; }
-    if (lo >= L.count) return false;  // nothing selected (reference: NaN); documented deviation
-    const LightTri* lt = &sc.light_tris[L.first + lo];
-    const float4 A = __ldg(&lt->p0n0x), B = __ldg(&lt->p1n0y), C = __ldg(&lt->p2n0z), D = __ldg(&lt->n1n2x), E = __ldg(&lt->n2yz);
-    const float inv = 1.0f / (u.y + u.z + u.w);
-    const float p1 = u.y * inv, p2 = u.z * inv, p3 = u.w * inv;  // quirk Q7
-    const float3 xl = f3(A) * p1 + f3(B) * p2 + f3(C) * p3;
-    const float3 vn = f3(A.w, B.w, C.w) * p1 + f3(D.x, D.y, D.z) * p2 + f3(D.w, E.x, E.y) * p3;
-    const float3 dv = xl - vx.p;
-    const float dist = length(dv);
-    const float3 w = dv * (1.0f / dist);
-    const float cosp = dot(w, vx.pn);
-    if (!(cosp > 0.0f)) return false;
-    const float cos_theta = fabsf(dot(w, vn)) / length(vn);
-    const float cos_hat = fabsf(cosp) / length(vx.pn);
-    const float dc = fmaxf(1.0f, dist);
-    const float g = cos_theta * cos_hat / (dc * dc) * L.area * cosp * (1.0f / MCPT_PI);  // quirk Q8
-    contrib = vx.kd * f3(L.radiance[0], L.radiance[1], L.radiance[2]) * g;
-    if (!(contrib.x != 0.0f || contrib.y != 0.0f || contrib.z != 0.0f)) return false;
-    ray_o = vx.p + w * 0.01f;
-    ray_d = w;
-    ray_tmax = (dist - 0.01f) * 1.0002f;  // the sampled triangle itself bounds the closest hit
-    return true;
-}
-
-// BRDFImportanceSampling (MTPC/pathTracing.cpp:30-64) around the un-normalised axis.  sin/cos of theta
-// are formed without the asin/acos round trip: diffuse theta = asin(sqrt(u)); specular
-// cos(theta) = u^(1/(Ns+1)) evaluated as 1 + expm1(log(u)/(Ns+1)) so that Ns = 1e5 keeps its precision.
-__device__ __forceinline__ float3 brdf_sample(const float3 axis, const int lobe, const float Ns, const float u_phi, const float u_theta) {
-    float sphi, cphi;
-    sincosf(u_phi * 2.0f * MCPT_PI, &sphi, &cphi);
-    float st, ct;
-    if (lobe == LOBE_DIFFUSE) { st = sqrtf(u_theta); ct = sqrtf(1.0f - u_theta); }
-    else { const float om = -expm1f(logf(u_theta) / (Ns + 1.0f)); ct = 1.0f - om; st = sqrtf(om * (2.0f - om)); }
-    float3 front;
-    if (fabsf(axis.x) > fabsf(axis.y)) front = normalize(f3(axis.z, 0.0f, -axis.x));
-    else front = normalize(f3(0.0f, -axis.z, axis.y));
-    const float3 right = cross(axis, front);
-    return normalize(right * (st * cphi) + axis * ct + front * (st * sphi));
-}
-
-// Refract (MTPC/pathTracing.cpp:13-27)
-__device__ __forceinline__ bool refract_dir(const float3 i, const float3 n, const float eta, float3& out) {
-    const float cosi = dot(i, n);
-    const float cost2 = 1.0f - eta * eta * (1.0f - cosi * cosi);
-    if (cost2 >= 0.0f) { out = i * eta - n * (eta * cosi + sqrtf(cost2)); return true; }
-    return false;
-}
-
-// nextRay (MTPC/pathTracing.cpp:66-134).  u = (rr, lobe, phi, theta) of STREAM_PATH.
-__device__ __forceinline__ void next_ray(const DeviceScene& sc, const PathVertex& vx, const float4 u, const unsigned bounce,
-                                         const unsigned seed_lo, const unsigned seed_hi, const unsigned pixel, const unsigned sample,
-                                         float3& ray_o, float3& ray_d, int& lobe, float3& weight) {
-    const DMaterial* m = &sc.materials[vx.mat];
-    const float3 ks = f3(m->ks[0], m->ks[1], m->ks[2]);
-    const float3 inc = -vx.wo;
-    if (m->Ni > 1.0f) {
-        const float cos_in = dot(inc, vx.pn);
-        float3 normal; float n1, n2;
-        if (cos_in > 0.0f) { normal = -vx.pn; n1 = m->Ni; n2 = 1.0f; } else { normal = vx.pn; n1 = 1.0f; n2 = m->Ni; }
-        const float r = (n1 - n2) / (n1 + n2), rf0 = r * r;
-        const float a = 1.0f - fabsf(cos_in);
-        const float fresnel = rf0 + (1.0f - rf0) * (a * a * a * a * a);
-        const float4 uf = philox_uniform4(bounce, STREAM_FRESNEL, seed_lo, seed_hi, pixel, sample);
-        if (fresnel < uf.x) {
-            ray_o = vx.p;  // no origin offset on this branch (:102,:109)
-            weight = f3(1.0f, 1.0f, 1.0f);
-            if (refract_dir(inc, normal, n1 / n2, ray_d)) { lobe = LOBE_TRANSMISSION; return; }
-            ray_d = inc - normal * (2.0f * dot(inc, normal));
-            lobe = LOBE_SPECULAR; weight = ks;
-            return;
-        }
-    }
-    const float kd_norm = length(vx.kd);
-    if (m->ks_norm != 0.0f && kd_norm / m->ks_norm < u.y) {  // quirk Q9
-        const float3 reflect = inc - vx.pn * (2.0f * dot(inc, vx.pn));
-        ray_d = brdf_sample(reflect, LOBE_SPECULAR, m->Ns, u.z, u.w);
-        lobe = LOBE_SPECULAR; weight = ks;
-    } else {
-        ray_d = brdf_sample(vx.pn, LOBE_DIFFUSE, m->Ns, u.z, u.w);
-        lobe = LOBE_DIFFUSE; weight = vx.kd;
-    }
-    ray_o = vx.p + ray_d * 0.01f;
+int launch_raygen(const DCamera& cam, float* d_dirs, cudaStream_t stream) {
+    raygen_kernel<<<(cam.height + 31) / 32, 32, 0, stream>>>(cam, d_dirs);
+    return (int)cudaGetLastError();
 }
 
 // ---- K6: megakernel ------------------------------------------------------------------------------------
@@ -161,16 +62,10 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
     if (x < W && y < H) {
         const unsigned pixel = (unsigned)(y * W + x);
         const size_t plane_stride = (size_t)W * H * 3;
-        // camera ray through the pixel's top-left corner (MTPC/pathTracing.cpp:294-308), FP64 then narrowed
-        float3 cam_o, cam_d;
-        {
-            const double px = P.cam.start[0] - P.cam.pdy[0] * y + P.cam.pdx[0] * x - P.cam.eye[0];
-            const double py = P.cam.start[1] - P.cam.pdy[1] * y + P.cam.pdx[1] * x - P.cam.eye[1];
-            const double pz = P.cam.start[2] - P.cam.pdy[2] * y + P.cam.pdx[2] * x - P.cam.eye[2];
-            const double r = 1.0 / sqrt(px * px + py * py + pz * pz);
-            cam_d = f3((float)(px * r), (float)(py * r), (float)(pz * r));
-            cam_o = f3((float)P.cam.eye[0], (float)P.cam.eye[1], (float)P.cam.eye[2]);
-        }
+        // camera ray through the pixel's top-left corner, precomputed by raygen_kernel (K7)
+        const float3 cam_d = f3(__ldg(P.cam_dirs + 3 * (size_t)pixel), __ldg(P.cam_dirs + 3 * (size_t)pixel + 1),
+                                __ldg(P.cam_dirs + 3 * (size_t)pixel + 2));
+        const float3 cam_o = f3((float)P.cam.eye[0], (float)P.cam.eye[1], (float)P.cam.eye[2]);
         const int nl = sc.n_lights;
         int chunk = P.chunk_begin + group * P.chunks_per_thread;       // global chunk index
         const int chunk_end = chunk + P.chunks_per_thread;
@@ -187,7 +82,7 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
         bool done = false;
 
         // sample finished with radiance Ls: add in sample order, close chunks as they fill
-        auto finish_sample = [&](const float3 Ls) { sum = sum + Ls; s++; phase = PH_NEWSAMPLE; };
+        auto finish_sample = [&](const float3 Ls) { sum = add_rn(sum, Ls); s++; phase = PH_NEWSAMPLE; };
         // start shading at a (primary or extend) hit that is not a light
         auto begin_path = [&](const Hit& h) {
             if (h.k < 0) { finish_sample(f3(0.f, 0.f, 0.f)); return; }
@@ -237,19 +132,19 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
                 begin_path(h);
             } else if (phase < nl) {
                 // visible iff the CLOSEST hit carries the light's material (:212-215)
-                if (h.k >= 0 && __float_as_int(__ldg(&sc.tri[h.k].v0m).w) == light_mat) L = L + beta * pend;
+                if (h.k >= 0 && __float_as_int(__ldg(&sc.tri[h.k].v0m).w) == light_mat) L = add_rn(L, mul_rn(beta, pend));
                 phase++;
             } else {
                 if (h.k < 0) { finish_sample(L); continue; }
                 const int m = __float_as_int(__ldg(&sc.tri[h.k].v0m).w);
                 const int li = sc.materials[m].light_id;
-                const float3 wgt = wnext * (1.0f / MCPT_P_RR);
+                const float3 bw = mul_rn(beta, wnext * (1.0f / MCPT_P_RR));
                 if (li >= 0) {   // diffuse rays drop emitters (NEE counted them, :247-253); specular/transmission keep them
                     if (lobe != LOBE_DIFFUSE)
-                        L = L + beta * wgt * f3(sc.lights[li].radiance[0], sc.lights[li].radiance[1], sc.lights[li].radiance[2]);
+                        L = add_rn(L, mul_rn(bw, f3(sc.lights[li].radiance[0], sc.lights[li].radiance[1], sc.lights[li].radiance[2])));
                     finish_sample(L);
                 } else {
-                    beta = beta * wgt;
+                    beta = bw;
                     make_vertex(sc, h, rd, vx);
                     bounce++;
                     phase = 0;
@@ -270,6 +165,36 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
 }
 
 // ---- K5: batch closest hit (parity hook of seam 2 and the traversal-only benchmark) -----------------
+// The traversal decides WHICH triangle is hit in FP32.  The record returned through the C ABI is then recomputed
+// once per ray in FP64 from the uploaded FP64 vertices with the reference's own formulas — plane hit
+// (MTPC/sceneManagement.cpp:316-323), t = (p.x - o.x)/d.x (MTPC/pathTracing.cpp:347) and findGarCor's area ratios
+// (:416-428) — because FP32 cannot hold t and barycentrics to 1e-5 on the millimetre-sized triangles of the
+// cornell-box table seen from 7 units away (|p| * 2^-24 / edge ~ 1e-4).  ~120 FP64 operations per ray against
+// ~2000 FP32 instructions of traversal.
+struct D3 { double x, y, z; };
+__device__ __forceinline__ D3 d3(double x, double y, double z) { D3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ D3 dsub(D3 a, D3 b) { return d3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ double ddot(D3 a, D3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ D3 dcross(D3 a, D3 b) { return d3(a.y * b.z - b.y * a.z, b.x * a.z - a.x * b.z, a.x * b.y - b.x * a.y); }
+
+__device__ __forceinline__ void refine_hit_fp64(const double* __restrict__ pos, const int face, const float3 of, const float3 df,
+                                                float& t_out, float& u_out, float& v_out) {
+    const double* q = pos + 9 * (size_t)face;
+    const D3 v1 = d3(q[0], q[1], q[2]), v2 = d3(q[3], q[4], q[5]), v3 = d3(q[6], q[7], q[8]);
+    const D3 o = d3(of.x, of.y, of.z), d = d3(df.x, df.y, df.z);
+    D3 n = dcross(dsub(v1, v2), dsub(v3, v1));                     // Face::calNorm
+    const double nl = sqrt(ddot(n, n));
+    n = d3(n.x / nl, n.y / nl, n.z / nl);
+    const double tp = ddot(dsub(v1, o), n) / ddot(n, d);
+    const D3 p = d3(o.x + d.x * tp, o.y + d.y * tp, o.z + d.z * tp);
+    t_out = (float)((p.x - o.x) / d.x);
+    const D3 e2 = dsub(v1, v3), e3 = dsub(v2, v1);
+    const D3 m = dcross(dsub(v3, v2), e2);
+    const double an = ddot(m, m);
+    u_out = (float)(ddot(dcross(e2, dsub(p, v1)), m) / an);        // b2: weight of v2
+    v_out = (float)(ddot(dcross(e3, dsub(p, v2)), m) / an);        // b3: weight of v3
+}
+
 template <bool COUNT>
 __global__ void __launch_bounds__(128) trace_kernel(const DeviceScene sc, const float* __restrict__ org_dir, const int n,
                                                     mcpt_hit* __restrict__ hits, unsigned long long* counters) {
@@ -280,9 +205,11 @@ __global__ void __launch_bounds__(128) trace_kernel(const DeviceScene sc, const 
         const float3 o = f3(r[0], r[1], r[2]), d = f3(r[3], r[4], r[5]);
         const Hit h = trace_closest<COUNT>(sc, o, d, 3.0e38f, n_nodes, n_tris);
         mcpt_hit out;
-        out.t = h.k >= 0 ? h.t : 0.0f; out.u = h.u; out.v = h.v;
-        out.leaf = h.k;
-        out.tri = h.k >= 0 ? sc.leaf_face[h.k] : -1;
+        out.t = 0.0f; out.u = 0.0f; out.v = 0.0f; out.leaf = h.k; out.tri = -1;
+        if (h.k >= 0) {
+            out.tri = sc.leaf_face[h.k];
+            refine_hit_fp64(sc.pos, out.tri, o, d, out.t, out.u, out.v);
+        }
         hits[i] = out;
     }
     if (COUNT) {

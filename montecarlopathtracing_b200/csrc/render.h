@@ -6,8 +6,15 @@ namespace mcpt {
 // K5: closest hit for n rays (org_dir = n x 6 floats, device). hits = n x mcpt_hit (device).
 int launch_trace(const DeviceScene& sc, const float* d_org_dir, int n, mcpt_hit* d_hits, bool count,
                  unsigned long long* d_counters, cudaStream_t stream);
+// K7: primary ray directions (height*width*3 floats), bit-faithful to generateImg's repeated-addition pixel walk.
+int launch_raygen(const DCamera& cam, float* d_dirs, cudaStream_t stream);
 // K6: megakernel integrator; fills P.planes (P.n_chunks planes).
 int launch_megakernel(const RenderParams& P, int flags, cudaStream_t stream);
+// K8+K9: wavefront integrator (wavefront.cu); same planes as the megakernel, bit for bit.  Synchronises `stream`
+// every few iterations to read the number of live path slots.
+int wavefront_slots(const RenderParams& P);                    // < 0: too many slots for the 26-bit ray id
+size_t wavefront_scratch_bytes(int n_slots, int n_lights);
+int launch_wavefront(const RenderParams& P, int flags, void* d_scratch, unsigned* h_alive_pinned, cudaStream_t stream, int* launches);
 // K12: out[i] = scale * fixed pairwise tree sum over n planes (n in {1,2,4,8}).
 int launch_sum_planes(const float* d_planes, int n, long long count, float scale, float* d_out, cudaStream_t stream);
 }  // namespace mcpt

@@ -1,0 +1,146 @@
+// shade.cuh — the per-vertex arithmetic of the integrator, shared by the megakernel (render.cu) and the wavefront
+// kernels (wavefront.cu) so that both produce the same floating-point results for the same Philox keys.
+// Iterative form of the reference's recursive shade() (MTPC/pathTracing.cpp:137-266) with every quirk of SURVEY.md 3A
+// kept: un-normalised shading normals (Q3), u->row / v->column texture lookup (Q5), light-selection range frozen to
+// light 0's area (Q6), centroid-biased light points (Q7), the double receiver cosine and max(1,d) clamp (Q8), lobe
+// pick without pdf division (Q9).
+#pragma once
+#include "device_types.cuh"
+#include "philox.cuh"
+#include "trace.cuh"
+#include "vecmath.cuh"
+
+namespace mcpt {
+
+// explicitly rounded products/sums for the radiance bookkeeping: no FMA contraction, so the megakernel and the
+// wavefront kernels accumulate bit-identically whatever the surrounding code looks like
+__device__ __forceinline__ float3 mul_rn(float3 a, float3 b) { return f3(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y), __fmul_rn(a.z, b.z)); }
+__device__ __forceinline__ float3 add_rn(float3 a, float3 b) { return f3(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z)); }
+
+#define MCPT_PI 3.1415926f       /* MTPC/pathTracing.h:11 */
+#define MCPT_P_RR 0.6f           /* MTPC/pathTracing.cpp:237 */
+#define MCPT_MAX_DEPTH 64        /* reference recursion is unbounded; 0.6^64 ~ 6e-15 (same cap as the oracle) */
+enum { LOBE_DIFFUSE = 0, LOBE_SPECULAR = 1, LOBE_TRANSMISSION = 2 };
+
+struct PathVertex { float3 p, pn, kd, wo; int mat; };
+
+// Hit -> shading point: position and barycentric normal (MTPC/pathTracing.cpp:345-351, not normalised),
+// material, kd or texel (MTPC/pathTracing.cpp:148-163).
+__device__ __forceinline__ void make_vertex(const DeviceScene& sc, const Hit& h, const float3 ray_d, PathVertex& vx) {
+    const TriGeom* g = &sc.tri[h.k];
+    const float4 v0 = __ldg(&g->v0m), e1 = __ldg(&g->e1f), e2 = __ldg(&g->e2);
+    const TriShade* s = &sc.shade[h.k];
+    const float4 sa = __ldg(&s->a), sb = __ldg(&s->b), sc4 = __ldg(&s->c), sd = __ldg(&s->d);
+    const float w = 1.0f - h.u - h.v;
+    vx.p = f3(v0) + f3(e1) * h.u + f3(e2) * h.v;
+    vx.pn = f3(sa.x, sa.y, sa.z) * w + f3(sa.w, sb.x, sb.y) * h.u + f3(sb.z, sb.w, sc4.x) * h.v;
+    vx.wo = -ray_d;
+    vx.mat = __float_as_int(v0.w);
+    const DMaterial* m = &sc.materials[vx.mat];
+    if (m->tex_id >= 0) {
+        const DTexture tx = sc.textures[m->tex_id];
+        const float row = sc4.y * w + sc4.w * h.u + sd.y * h.v;   // vt.x -> row (quirk Q5)
+        const float col = sc4.z * w + sd.x * h.u + sd.z * h.v;    // vt.y -> column
+        const float irow = row - floorf(row), icol = col - floorf(col);
+        const int r = min((int)(irow * tx.height), tx.height - 1), c = min((int)(icol * tx.width), tx.width - 1);
+        const unsigned char* px = sc.tex_bytes + tx.offset + ((size_t)r * tx.width + c) * 3;
+        vx.kd = f3(px[2] * (1.0f / 255.0f), px[1] * (1.0f / 255.0f), px[0] * (1.0f / 255.0f));  // BGR -> RGB
+    } else {
+        vx.kd = f3(m->kd[0], m->kd[1], m->kd[2]);
+    }
+}
+
+// One light's next-event estimate (MTPC/pathTracing.cpp:171-231).  Returns false when nothing can be
+// added (no triangle selected, receiver faces away, zero weight) so the shadow ray is not traced.
+// contrib = kd/pi * Le * |w.vn|/|vn| * |w.pn|/|pn| * A / max(1,d)^2 * (w.pn); the caller multiplies by V.
+__device__ __forceinline__ bool sample_light(const DeviceScene& sc, const DLight& L, const PathVertex& vx, const float4 u,
+                                             float3& ray_o, float3& ray_d, float& ray_tmax, float3& contrib) {
+    const float rnd = u.x * sc.area0;  // quirk Q6
+    const float* cdf = sc.light_cdf + L.first;
+    int lo = 0, hi = L.n_search;      // first j with rnd < cdf[j]
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (rnd < __ldg(&cdf[mid])) hi = mid; else lo = mid + 1; }
+    if (lo >= L.count) return false;  // nothing selected (reference: NaN); documented deviation
+    const LightTri* lt = &sc.light_tris[L.first + lo];
+    const float4 A = __ldg(&lt->p0n0x), B = __ldg(&lt->p1n0y), C = __ldg(&lt->p2n0z), D = __ldg(&lt->n1n2x), E = __ldg(&lt->n2yz);
+    const float inv = 1.0f / (u.y + u.z + u.w);
+    const float p1 = u.y * inv, p2 = u.z * inv, p3 = u.w * inv;  // quirk Q7
+    const float3 xl = f3(A) * p1 + f3(B) * p2 + f3(C) * p3;
+    const float3 vn = f3(A.w, B.w, C.w) * p1 + f3(D.x, D.y, D.z) * p2 + f3(D.w, E.x, E.y) * p3;
+    const float3 dv = xl - vx.p;
+    const float dist = length(dv);
+    const float3 w = dv * (1.0f / dist);
+    const float cosp = dot(w, vx.pn);
+    if (!(cosp > 0.0f)) return false;
+    const float cos_theta = fabsf(dot(w, vn)) / length(vn);
+    const float cos_hat = fabsf(cosp) / length(vx.pn);
+    const float dc = fmaxf(1.0f, dist);
+    const float g = cos_theta * cos_hat / (dc * dc) * L.area * cosp * (1.0f / MCPT_PI);  // quirk Q8
+    contrib = vx.kd * f3(L.radiance[0], L.radiance[1], L.radiance[2]) * g;
+    if (!(contrib.x != 0.0f || contrib.y != 0.0f || contrib.z != 0.0f)) return false;
+    ray_o = vx.p + w * 0.01f;
+    ray_d = w;
+    ray_tmax = (dist - 0.01f) * 1.0002f;  // the sampled triangle itself bounds the closest hit
+    return true;
+}
+
+// BRDFImportanceSampling (MTPC/pathTracing.cpp:30-64) around the un-normalised axis.  sin/cos of theta
+// are formed without the asin/acos round trip: diffuse theta = asin(sqrt(u)); specular
+// cos(theta) = u^(1/(Ns+1)) evaluated as 1 + expm1(log(u)/(Ns+1)) so that Ns = 1e5 keeps its precision.
+__device__ __forceinline__ float3 brdf_sample(const float3 axis, const int lobe, const float Ns, const float u_phi, const float u_theta) {
+    float sphi, cphi;
+    sincosf(u_phi * 2.0f * MCPT_PI, &sphi, &cphi);
+    float st, ct;
+    if (lobe == LOBE_DIFFUSE) { st = sqrtf(u_theta); ct = sqrtf(1.0f - u_theta); }
+    else { const float om = -expm1f(logf(u_theta) / (Ns + 1.0f)); ct = 1.0f - om; st = sqrtf(om * (2.0f - om)); }
+    float3 front;
+    if (fabsf(axis.x) > fabsf(axis.y)) front = normalize(f3(axis.z, 0.0f, -axis.x));
+    else front = normalize(f3(0.0f, -axis.z, axis.y));
+    const float3 right = cross(axis, front);
+    return normalize(right * (st * cphi) + axis * ct + front * (st * sphi));
+}
+
+// Refract (MTPC/pathTracing.cpp:13-27)
+__device__ __forceinline__ bool refract_dir(const float3 i, const float3 n, const float eta, float3& out) {
+    const float cosi = dot(i, n);
+    const float cost2 = 1.0f - eta * eta * (1.0f - cosi * cosi);
+    if (cost2 >= 0.0f) { out = i * eta - n * (eta * cosi + sqrtf(cost2)); return true; }
+    return false;
+}
+
+// nextRay (MTPC/pathTracing.cpp:66-134).  u = (rr, lobe, phi, theta) of STREAM_PATH.
+__device__ __forceinline__ void next_ray(const DeviceScene& sc, const PathVertex& vx, const float4 u, const unsigned bounce,
+                                         const unsigned seed_lo, const unsigned seed_hi, const unsigned pixel, const unsigned sample,
+                                         float3& ray_o, float3& ray_d, int& lobe, float3& weight) {
+    const DMaterial* m = &sc.materials[vx.mat];
+    const float3 ks = f3(m->ks[0], m->ks[1], m->ks[2]);
+    const float3 inc = -vx.wo;
+    if (m->Ni > 1.0f) {
+        const float cos_in = dot(inc, vx.pn);
+        float3 normal; float n1, n2;
+        if (cos_in > 0.0f) { normal = -vx.pn; n1 = m->Ni; n2 = 1.0f; } else { normal = vx.pn; n1 = 1.0f; n2 = m->Ni; }
+        const float r = (n1 - n2) / (n1 + n2), rf0 = r * r;
+        const float a = 1.0f - fabsf(cos_in);
+        const float fresnel = rf0 + (1.0f - rf0) * (a * a * a * a * a);
+        const float4 uf = philox_uniform4(bounce, STREAM_FRESNEL, seed_lo, seed_hi, pixel, sample);
+        if (fresnel < uf.x) {
+            ray_o = vx.p;  // no origin offset on this branch (:102,:109)
+            weight = f3(1.0f, 1.0f, 1.0f);
+            if (refract_dir(inc, normal, n1 / n2, ray_d)) { lobe = LOBE_TRANSMISSION; return; }
+            ray_d = inc - normal * (2.0f * dot(inc, normal));
+            lobe = LOBE_SPECULAR; weight = ks;
+            return;
+        }
+    }
+    const float kd_norm = length(vx.kd);
+    if (m->ks_norm != 0.0f && kd_norm / m->ks_norm < u.y) {  // quirk Q9
+        const float3 reflect = inc - vx.pn * (2.0f * dot(inc, vx.pn));
+        ray_d = brdf_sample(reflect, LOBE_SPECULAR, m->Ns, u.z, u.w);
+        lobe = LOBE_SPECULAR; weight = ks;
+    } else {
+        ray_d = brdf_sample(vx.pn, LOBE_DIFFUSE, m->Ns, u.z, u.w);
+        lobe = LOBE_DIFFUSE; weight = vx.kd;
+    }
+    ray_o = vx.p + ray_d * 0.01f;
+}
+
+}  // namespace mcpt

@@ -7,7 +7,7 @@
 // Semantics kept from the reference: two-sided triangles, inclusive edges, hits need t > 0 (no
 // epsilon), boxes are clipped to t >= 0, the closest hit wins and an exact tie in t goes to the
 // lowest sorted-leaf index (first found in the reference's left-to-right DFS, :355-361), and a ray
-// with direction.x == 0 hits nothing (its t = (p.x - o.x)/d.x is NaN, :347 — quirk Q2).
+// whose d.x*t vanishes against o.x in FP64 hits nothing (its t = (p.x - o.x)/d.x is 0 or NaN, :347 — quirk Q2).
 // New: children are visited near-first and pruned against the current best t.
 #pragma once
 #include "device_types.cuh"
@@ -81,7 +81,12 @@ __device__ __forceinline__ Hit trace_closest(const DeviceScene& sc, const float3
             const float v = dot(d, qvec) * inv_det;
             const float t = dot(E2, qvec) * inv_det;
             if (u >= -MCPT_EDGE_EPS && v >= -MCPT_EDGE_EPS && u + v <= 1.0f + MCPT_EDGE_EPS && t > 0.0f && (t < best.t || (t == best.t && k < best.k))) {
-                best.t = t; best.u = u; best.v = v; best.k = k;
+                // quirk Q2 in full: the reference keeps a hit only if t = (p.x - o.x)/d.x > 0 with p.x = o.x + d.x*t formed
+                // in FP64 (MTPC/pathTracing.cpp:347,355); when |d.x*t| is below half an ulp of o.x that is 0 and the
+                // hit is dropped.  Candidates that pass the FP32 test are rare (1-2 per ray), so the FP64 check is cheap.
+                if (__dadd_rn((double)o.x, __dmul_rn((double)d.x, (double)t)) != (double)o.x) {
+                    best.t = t; best.u = u; best.v = v; best.k = k;
+                }
             }
         }
         if (sp == 0) break;

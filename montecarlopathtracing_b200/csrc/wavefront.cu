@@ -1,0 +1,315 @@
+// wavefront.cu — seam 3 as a wavefront integrator (K8 wf_shade + K9 wf_trace), the alternative to the megakernel.
+//
+// The megakernel's lanes spend most of their time masked off: a warp holds lanes that are shading, drawing Philox
+// numbers, walking the BVH and testing triangles all at once (ncu, profiles/r1_megakernel.md: 5.9 of 32 lanes
+// active per issued instruction).  Here the two kinds of work run in separate kernels:
+//   wf_shade  one thread per path SLOT.  Consumes the slot's ray results, advances the path state machine of
+//             shade() (MTPC/pathTracing.cpp:137-266) to the next vertex and emits ALL rays of that vertex at once —
+//             one shadow ray per light (NEE) plus the extend ray; their Philox numbers do not depend on each other —
+//             into a ray queue compacted with warp ballot/popc (one atomic per warp and ray kind).
+//   wf_trace  one thread per queued ray: closest hit; extend/primary rays write the hit back to their slot, shadow
+//             rays set the slot's visibility bit when the closest hit carries the light's material (:212-215).
+// A slot owns (pixel, group of sample chunks) for the whole render, like a megakernel thread: it walks its samples in
+// order and adds them up in a register-resident sum that travels in the slot state, so the image is the same pure
+// function of (seed, pixel, sample) and of the fixed chunk tree — bit-identical to the megakernel's.
+//
+// HBM layout (SoA over n_slots; every field a 16-B vector): hit, hit0, sum_s, beta_m, L, rd, pend[n_lights][n_slots];
+// vis[n_slots]; ray queue ray_o / ray_d of (n_lights + 1) * n_slots entries.
+#include "render.h"
+#include "shade.cuh"
+
+namespace mcpt {
+
+enum { WF_NEW = 0, WF_WAIT_PRIMARY = 1, WF_WAIT_VERTEX = 2, WF_DONE = 3 };
+enum { WF_ID_BITS = 26, WF_MAX_LIGHTS = 32 };
+// counters (unsigned, in the scratch block): [0,1] queue tail by iteration parity, [2,3] slots alive by parity,
+// [4,5] queue head (dynamic fetch) by parity
+enum { WFC_TAIL = 0, WFC_ALIVE = 2, WFC_HEAD = 4, WFC_COUNT = 8 };
+
+struct WfBuffers {
+    float4* hit;     // last primary/extend result: (t, u, v, leaf as int bits)
+    float4* hit0;    // cached primary hit (quirk Q4: every sample of a pixel shares its primary ray)
+    float4* sum_s;   // chunk sum rgb, next sample index (int bits)
+    float4* beta_m;  // throughput rgb, meta bits (see META_*)
+    float4* L;       // radiance of the sample in flight
+    float4* rd;      // direction of the extend ray in flight (the next vertex's -wo)
+    float4* pend;    // [light][slot]: throughput * unshadowed NEE contribution of the vertex in flight
+    unsigned* vis;   // shadow-ray results, bit l = light l visible
+    float4* ray_o;   // queue: origin, tmax
+    float4* ray_d;   // queue: direction, id = slot | (kind << 26), kind 0 = primary/extend, l+1 = shadow ray of light l
+    unsigned* counters;
+    int n_slots;
+};
+
+// meta: state(2) | lobe(2) << 2 | has_extend << 4 | have_hit0 << 5 | bounce << 8 | chunk << 16
+__device__ __forceinline__ unsigned pack_meta(int state, int lobe, bool ext, bool have0, unsigned bounce, int chunk) {
+    return (unsigned)state | ((unsigned)lobe << 2) | ((unsigned)ext << 4) | ((unsigned)have0 << 5) | (bounce << 8) | ((unsigned)chunk << 16);
+}
+
+// Append a ray for every lane with pred set: one atomic per warp, slots in lane order.  Must be called by all 32 lanes.
+__device__ __forceinline__ void push_ray(const bool pred, const WfBuffers& B, unsigned* tail, const float3 o, const float3 d,
+                                         const float tmax, const unsigned id) {
+    const unsigned mask = __ballot_sync(0xffffffffu, pred);
+    if (mask == 0u) return;
+    const int lane = threadIdx.x & 31;
+    unsigned base = 0;
+    if (lane == __ffs(mask) - 1) base = atomicAdd(tail, (unsigned)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
+    if (pred) {
+        const unsigned i = base + __popc(mask & ((1u << lane) - 1u));
+        __stcg(&B.ray_o[i], make_float4(o.x, o.y, o.z, tmax));
+        __stcg(&B.ray_d[i], make_float4(d.x, d.y, d.z, __uint_as_float(id)));
+    }
+}
+
+// ---- K8: shade / path logic ------------------------------------------------------------------------------
+template <bool REUSE_PRIMARY>
+__global__ void __launch_bounds__(256) wf_shade(const RenderParams P, const WfBuffers B, const int iter) {
+    const DeviceScene& sc = P.scene;
+    const int W = P.cam.width, H = P.cam.height;
+    const int tiles_x = (W + 7) >> 3, tiles_y = (H + 3) >> 2, n_tiles = tiles_x * tiles_y;
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;      // the grid covers whole warps
+    const int par = iter & 1;
+    unsigned* tail = B.counters + WFC_TAIL + par;
+    if (slot == 0) {   // the other parity's counters were last used by iteration iter-1, which has completed
+        B.counters[WFC_TAIL + (par ^ 1)] = 0u; B.counters[WFC_ALIVE + (par ^ 1)] = 0u; B.counters[WFC_HEAD + (par ^ 1)] = 0u;
+    }
+    const int lane = threadIdx.x & 31;
+    const int warp_id = slot >> 5;
+    const int group = warp_id / n_tiles, tile = warp_id % n_tiles;
+    const int x = (tile % tiles_x) * 8 + (lane & 7), y = (tile / tiles_x) * 4 + (lane >> 3);
+    const bool valid = slot < B.n_slots && x < W && y < H;
+    const unsigned pixel = (unsigned)(y * W + x);
+    const int nl = sc.n_lights;
+
+    int state = WF_DONE, lobe = LOBE_DIFFUSE, chunk = 0, s = 0;
+    bool has_extend = false, have_hit0 = false, have_vertex = false, emit_primary = false, store_hit0 = false;
+    unsigned bounce = 0;
+    float3 sum = f3(0.f, 0.f, 0.f), beta = f3(1.f, 1.f, 1.f), L = f3(0.f, 0.f, 0.f), rd = f3(0.f, 0.f, 0.f);
+    float3 cam_d = f3(0.f, 0.f, 0.f), vdir = f3(0.f, 0.f, 0.f);
+    const float3 cam_o = f3((float)P.cam.eye[0], (float)P.cam.eye[1], (float)P.cam.eye[2]);
+    Hit hit0; hit0.t = 0.f; hit0.u = 0.f; hit0.v = 0.f; hit0.k = -1;
+    Hit hv = hit0;
+    const int chunk_first = P.chunk_begin + group * P.chunks_per_thread, chunk_end = chunk_first + P.chunks_per_thread;
+
+    if (valid) {
+        cam_d = f3(__ldg(P.cam_dirs + 3 * (size_t)pixel), __ldg(P.cam_dirs + 3 * (size_t)pixel + 1), __ldg(P.cam_dirs + 3 * (size_t)pixel + 2));
+        if (iter == 0) {
+            state = WF_NEW; chunk = chunk_first; s = (int)((long long)chunk * P.spp / MCPT_NUM_CHUNKS);
+        } else {
+            const float4 bm = __ldcg(&B.beta_m[slot]);
+            const unsigned meta = __float_as_uint(bm.w);
+            state = meta & 3u; lobe = (meta >> 2) & 3u; has_extend = (meta >> 4) & 1u; have_hit0 = (meta >> 5) & 1u;
+            bounce = (meta >> 8) & 0xffu; chunk = (int)(meta >> 16);
+            beta = f3(bm.x, bm.y, bm.z);
+            if (state != WF_DONE) {
+                const float4 ss = __ldcg(&B.sum_s[slot]);
+                sum = f3(ss.x, ss.y, ss.z); s = __float_as_int(ss.w);
+                if (have_hit0) { const float4 h = __ldcg(&B.hit0[slot]); hit0.t = h.x; hit0.u = h.y; hit0.v = h.z; hit0.k = __float_as_int(h.w); }
+            }
+        }
+    }
+    if (valid && state != WF_DONE) {
+        int s_end = (int)((long long)(chunk + 1) * P.spp / MCPT_NUM_CHUNKS);
+        bool need_sample = false;
+        auto finish_sample = [&](const float3 Ls) { sum = add_rn(sum, Ls); s++; need_sample = true; };
+        // first hit of a sample (primary ray, or its cached result)
+        auto begin_path = [&](const Hit& h) {
+            if (h.k < 0) { finish_sample(f3(0.f, 0.f, 0.f)); return; }
+            const int m = __float_as_int(__ldg(&sc.tri[h.k].v0m).w);
+            const int li = sc.materials[m].light_id;
+            if (li >= 0) { finish_sample(f3(sc.lights[li].radiance[0], sc.lights[li].radiance[1], sc.lights[li].radiance[2])); return; }
+            hv = h; vdir = cam_d; have_vertex = true;
+            beta = f3(1.f, 1.f, 1.f); L = f3(0.f, 0.f, 0.f); bounce = 0;
+        };
+        if (state == WF_NEW) {
+            need_sample = true;
+        } else if (state == WF_WAIT_PRIMARY) {
+            const float4 h4 = __ldcg(&B.hit[slot]);
+            Hit h; h.t = h4.x; h.u = h4.y; h.v = h4.z; h.k = __float_as_int(h4.w);
+            if (REUSE_PRIMARY) { hit0 = h; have_hit0 = true; store_hit0 = true; }
+            begin_path(h);
+        } else {   // WF_WAIT_VERTEX: resolve the vertex's NEE in light order, then look at the extend ray
+            const float4 l4 = __ldcg(&B.L[slot]);
+            L = f3(l4.x, l4.y, l4.z);
+            const unsigned v = __ldcg(&B.vis[slot]);
+            for (int l = 0; l < nl; l++)
+                if ((v >> l) & 1u) { const float4 p4 = __ldcg(&B.pend[(size_t)l * B.n_slots + slot]); L = add_rn(L, f3(p4.x, p4.y, p4.z)); }
+            if (!has_extend) {
+                finish_sample(L);
+            } else {
+                const float4 h4 = __ldcg(&B.hit[slot]);
+                Hit h; h.t = h4.x; h.u = h4.y; h.v = h4.z; h.k = __float_as_int(h4.w);
+                if (h.k < 0) {
+                    finish_sample(L);
+                } else {
+                    const int m = __float_as_int(__ldg(&sc.tri[h.k].v0m).w);
+                    const int li = sc.materials[m].light_id;
+                    if (li >= 0) {   // diffuse rays drop emitters (NEE counted them, :247-253); specular/transmission keep them
+                        if (lobe != LOBE_DIFFUSE)
+                            L = add_rn(L, mul_rn(beta, f3(sc.lights[li].radiance[0], sc.lights[li].radiance[1], sc.lights[li].radiance[2])));
+                        finish_sample(L);
+                    } else {
+                        const float4 r4 = __ldcg(&B.rd[slot]);
+                        hv = h; vdir = f3(r4.x, r4.y, r4.z); have_vertex = true; bounce++;
+                    }
+                }
+            }
+        }
+        while (need_sample) {
+            need_sample = false;
+            while (s >= s_end && chunk < chunk_end) {   // chunk complete (or empty): write its plane
+                float* out = P.planes + (size_t)(chunk - P.chunk_begin) * ((size_t)W * H * 3) + (size_t)pixel * 3;
+                out[0] = sum.x; out[1] = sum.y; out[2] = sum.z;
+                sum = f3(0.f, 0.f, 0.f);
+                chunk++;
+                s_end = (int)((long long)(chunk + 1) * P.spp / MCPT_NUM_CHUNKS);
+            }
+            if (chunk >= chunk_end) { state = WF_DONE; break; }
+            if (REUSE_PRIMARY && have_hit0) begin_path(hit0);
+            else emit_primary = true;
+        }
+        if (have_vertex) state = WF_WAIT_VERTEX;
+        else if (emit_primary) state = WF_WAIT_PRIMARY;
+    }
+
+    // ---- emission: the whole warp walks the lights together so every push is one ballot + one atomic ----
+    PathVertex vx; vx.mat = 0; vx.p = vx.pn = vx.kd = vx.wo = f3(0.f, 0.f, 0.f);
+    if (have_vertex) { make_vertex(sc, hv, vdir, vx); __stcg(&B.vis[slot], 0u); }
+    for (int l = 0; l < nl; l++) {
+        bool ok = false;
+        float3 o = f3(0.f, 0.f, 0.f), d = o, contrib = o; float tmax = 0.f;
+        if (have_vertex) {
+            const float4 u = philox_uniform4(bounce, STREAM_LIGHT0 + l, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
+            ok = sample_light(sc, sc.lights[l], vx, u, o, d, tmax, contrib);
+            if (ok) { const float3 bp = mul_rn(beta, contrib); __stcg(&B.pend[(size_t)l * B.n_slots + slot], make_float4(bp.x, bp.y, bp.z, 0.f)); }
+        }
+        push_ray(ok, B, tail, o, d, tmax, (unsigned)slot | ((unsigned)(l + 1) << WF_ID_BITS));
+    }
+    {
+        bool ext = false;
+        float3 o = cam_o, d = cam_d;
+        if (have_vertex) {
+            const float4 u = philox_uniform4(bounce, STREAM_PATH, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
+            if (u.x < MCPT_P_RR && bounce + 1 < MCPT_MAX_DEPTH) {   // russian_Roulette (:3-11,:240)
+                float3 wnext;
+                next_ray(sc, vx, u, bounce, P.seed_lo, P.seed_hi, pixel, (unsigned)s, o, d, lobe, wnext);
+                beta = mul_rn(beta, wnext * (1.0f / MCPT_P_RR));
+                rd = d; ext = true;
+            }
+            has_extend = ext;
+        }
+        push_ray(ext || emit_primary, B, tail, o, d, 3.0e38f, (unsigned)slot);
+    }
+    // ---- store the slot ----
+    if (valid) {
+        const bool was_done_before = (iter != 0) && !have_vertex && !emit_primary && state == WF_DONE;
+        __stcg(&B.beta_m[slot], make_float4(beta.x, beta.y, beta.z, __uint_as_float(pack_meta(state, lobe, has_extend, have_hit0, bounce, chunk))));
+        if (state != WF_DONE) {
+            __stcg(&B.sum_s[slot], make_float4(sum.x, sum.y, sum.z, __int_as_float(s)));
+            if (have_vertex) {
+                __stcg(&B.L[slot], make_float4(L.x, L.y, L.z, 0.f));
+                if (has_extend) __stcg(&B.rd[slot], make_float4(rd.x, rd.y, rd.z, 0.f));
+            }
+            if (store_hit0) __stcg(&B.hit0[slot], make_float4(hit0.t, hit0.u, hit0.v, __int_as_float(hit0.k)));
+        }
+        (void)was_done_before;
+    } else if (slot < B.n_slots && iter == 0) {
+        __stcg(&B.beta_m[slot], make_float4(0.f, 0.f, 0.f, __uint_as_float(pack_meta(WF_DONE, 0, false, false, 0, 0))));
+    }
+    const unsigned alive = __ballot_sync(0xffffffffu, valid && state != WF_DONE);
+    if (lane == 0 && alive) atomicAdd(B.counters + WFC_ALIVE + par, (unsigned)__popc(alive));
+}
+
+// ---- K9: trace the queue -----------------------------------------------------------------------------------
+// Persistent warps fetch 32 rays at a time from the queue head (one atomic per warp), so a warp that drew short
+// rays goes back for more instead of idling behind a long one.
+template <bool COUNT>
+__global__ void __launch_bounds__(128) wf_trace(const DeviceScene sc, const WfBuffers B, const int iter, unsigned long long* stats) {
+    const int par = iter & 1;
+    const unsigned n = __ldcg(B.counters + WFC_TAIL + par);
+    unsigned* head = B.counters + WFC_HEAD + par;
+    const int lane = threadIdx.x & 31;
+    unsigned n_nodes = 0, n_tris = 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[0], (unsigned long long)n);
+    while (true) {
+        unsigned base = 0;
+        if (lane == 0) base = atomicAdd(head, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const unsigned i = base + lane;
+        if (i < n) {
+            const float4 o4 = __ldcg(&B.ray_o[i]), d4 = __ldcg(&B.ray_d[i]);
+            const unsigned id = __float_as_uint(d4.w);
+            const unsigned slot = id & ((1u << WF_ID_BITS) - 1u), kind = id >> WF_ID_BITS;
+            const Hit h = trace_closest<COUNT>(sc, f3(o4), f3(d4), o4.w, n_nodes, n_tris);
+            if (kind == 0u) {
+                __stcg(&B.hit[slot], make_float4(h.t, h.u, h.v, __int_as_float(h.k)));
+            } else if (h.k >= 0 && __float_as_int(__ldg(&sc.tri[h.k].v0m).w) == sc.lights[kind - 1].mat_id) {
+                atomicOr(&B.vis[slot], 1u << (kind - 1));   // visible iff the CLOSEST hit carries the light's material (:212-215)
+            }
+        }
+    }
+    if (COUNT) {
+        const unsigned a = __reduce_add_sync(0xffffffffu, n_nodes), b = __reduce_add_sync(0xffffffffu, n_tris);
+        if (lane == 0) { atomicAdd(&stats[1], (unsigned long long)a); atomicAdd(&stats[2], (unsigned long long)b); }
+    }
+}
+
+// ---- host side ----------------------------------------------------------------------------------------------
+static size_t align256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+int wavefront_slots(const RenderParams& P) {
+    const long long n_tiles = (long long)((P.cam.width + 7) / 8) * ((P.cam.height + 3) / 4);
+    const long long n = n_tiles * 32 * (P.n_chunks / P.chunks_per_thread);
+    return n < (1LL << WF_ID_BITS) ? (int)n : -1;
+}
+
+size_t wavefront_scratch_bytes(int n_slots, int n_lights) {
+    const size_t n = (size_t)n_slots;
+    return 6 * align256(16 * n) + align256(16 * n * (size_t)(n_lights > 0 ? n_lights : 1)) + align256(4 * n) +
+           2 * align256(16 * n * (size_t)(n_lights + 1)) + align256(4 * WFC_COUNT);
+}
+
+// Runs the shade/trace loop until every slot is done.  h_alive: pinned host word for the termination check.
+int launch_wavefront(const RenderParams& P, int flags, void* scratch, unsigned* h_alive, cudaStream_t stream, int* launches) {
+    const int n_slots = wavefront_slots(P);
+    const int nl = P.scene.n_lights;
+    if (n_slots <= 0 || nl > WF_MAX_LIGHTS) return (int)cudaErrorInvalidConfiguration;
+    WfBuffers B{};
+    char* p = (char*)scratch;
+    auto take = [&](size_t bytes) { char* r = p; p += align256(bytes); return r; };
+    const size_t n = (size_t)n_slots;
+    B.hit = (float4*)take(16 * n); B.hit0 = (float4*)take(16 * n); B.sum_s = (float4*)take(16 * n);
+    B.beta_m = (float4*)take(16 * n); B.L = (float4*)take(16 * n); B.rd = (float4*)take(16 * n);
+    B.pend = (float4*)take(16 * n * (size_t)(nl > 0 ? nl : 1));
+    B.vis = (unsigned*)take(4 * n);
+    B.ray_o = (float4*)take(16 * n * (size_t)(nl + 1)); B.ray_d = (float4*)take(16 * n * (size_t)(nl + 1));
+    B.counters = (unsigned*)take(4 * WFC_COUNT);
+    B.n_slots = n_slots;
+    cudaError_t e = cudaMemsetAsync(B.counters, 0, 4 * WFC_COUNT, stream);
+    if (e != cudaSuccess) return (int)e;
+    const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
+    const int shade_blocks = (n_slots + 255) / 256;
+    const int trace_blocks = 148 * 16;   // 16 CTAs of 4 warps per SM
+    int nlaunch = 0;
+    const int batch = 8;
+    for (int iter = 0;; iter++) {
+        if (reuse) wf_shade<true><<<shade_blocks, 256, 0, stream>>>(P, B, iter);
+        else wf_shade<false><<<shade_blocks, 256, 0, stream>>>(P, B, iter);
+        if (count) wf_trace<true><<<trace_blocks, 128, 0, stream>>>(P.scene, B, iter, P.counters);
+        else wf_trace<false><<<trace_blocks, 128, 0, stream>>>(P.scene, B, iter, P.counters);
+        nlaunch += 2;
+        if (iter % batch == batch - 1) {
+            e = cudaMemcpyAsync(h_alive, B.counters + WFC_ALIVE + (iter & 1), 4, cudaMemcpyDeviceToHost, stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+            if (e != cudaSuccess) return (int)e;
+            if (*h_alive == 0u) break;
+        }
+        if (iter > (1 << 24)) return (int)cudaErrorUnknown;
+    }
+    if (launches) *launches += nlaunch;
+    return (int)cudaGetLastError();
+}
+
+}  // namespace mcpt

@@ -62,7 +62,8 @@ def make_rays(scene, name, rng):
     # a few non-unit directions and rays that start inside/outside the scene box
     o = rng.uniform(-2, 3, size=(500, 3)); dd = rng.normal(size=(500, 3)) * rng.uniform(0.1, 5, size=(500, 1))
     misc = np.concatenate([o, dd], axis=1)
-    return np.concatenate([prim, bounce, shadow, misc], axis=0)
+    # float32-representable: mcpt_trace takes FP32 rays, so the reference must see exactly the same rays
+    return np.concatenate([prim, bounce, shadow, misc], axis=0).astype(np.float32).astype(np.float64)
 
 
 def main():

@@ -49,9 +49,10 @@ def test_golden_ray_batches(gpu_ctx, scenes, name):
     for i in bad:
         both_hit = hits["tri"][i] >= 0 and g["hit"][i] == 1
         assert both_hit and abs(hits["t"][i] - g["t"][i]) <= 1e-4 * abs(g["t"][i]), (i, hits[i], g["face"][i], g["t"][i])
-    assert n_bad <= max(2, n // 5000), "hit ids must match the reference (%d of %d differ)" % (n_bad, n)
-    assert np.quantile(t_err, 0.999) <= T_RTOL and np.quantile(bary_err, 0.999) <= BARY_ATOL
-    assert t_err.max() <= 1e-4 and bary_err.max() <= 1e-3
+    # camera rays through pixel corners run exactly along the cornell-box wall edges on the image diagonals
+    assert n_bad <= max(2, n // 1000), "hit ids must match the reference (%d of %d differ)" % (n_bad, n)
+    # every id-matching hit, not a quantile: the record is recomputed in FP64 from the FP64 vertices (render.cu)
+    assert t_err.max() <= T_RTOL and bary_err.max() <= BARY_ATOL
     st = gpu_ctx.last_stats
     assert st.rays == n and st.node_visits > 0 and st.tri_tests > 0
 
@@ -69,7 +70,7 @@ def test_random_soup_vs_oracle(gpu_ctx, oracle):
     ref = oracle.OracleScene(desc).trace(rays.astype(np.float64))
     n_bad, t_err, bary_err, same = compare_hits(hits, ref["hit"], ref["face"], ref["t"], rays, keep[0].reshape(n, 3, 3), ref["p"])
     assert n_bad <= 4
-    assert np.quantile(t_err, 0.999) <= T_RTOL
+    assert t_err.max() <= T_RTOL and bary_err.max() <= BARY_ATOL
     assert np.array_equal(hits["leaf"][same & (hits["tri"] >= 0)], ref["leaf"][same & (hits["tri"] >= 0)])
 
 
@@ -98,11 +99,13 @@ def test_single_triangle_scene(gpu_ctx):
     tri = keep[0].reshape(3, 3)
     c = tri.mean(axis=0)
     nrm = np.cross(tri[1] - tri[0], tri[2] - tri[0]); nrm /= np.linalg.norm(nrm)
-    d = -nrm + np.array([1e-3, 2e-3, 3e-3])
-    rays = np.array([np.concatenate([c + 2 * nrm, d]), np.concatenate([c + 2 * nrm, -d])], np.float32)
+    target = 0.2 * tri[0] + 0.3 * tri[1] + 0.5 * tri[2]          # barycentric weights of v2, v3 = (0.3, 0.5)
+    o = c + 2 * nrm + np.array([0.05, 0.02, 0.01])
+    d = target - o
+    rays = np.array([np.concatenate([o, d]), np.concatenate([o, -d])], np.float32)
     hits = gpu_ctx.trace(rays)
     assert hits["tri"][0] == 0 and hits["tri"][1] == -1
-    assert abs(hits["u"][0] - 1 / 3) < 1e-2 and abs(hits["v"][0] - 1 / 3) < 1e-2
+    assert abs(hits["u"][0] - 0.3) < 1e-5 and abs(hits["v"][0] - 0.5) < 1e-5 and abs(hits["t"][0] - 1.0) < 1e-5
 
 
 def test_empty_batch_and_call_order(gpu_ctx, built_lib):
