@@ -156,7 +156,8 @@ def run_ours(args):
     ctx.set_stream(stream.cuda_stream)                       # our kernels and torch's collectives share one stream
     ctx.set_seed(2026)
     ctx.upload_scene(desc)
-    render_partial, sum_partials, stats = gpu_backend(ctx, s.camera, spp, w, h)
+    mode = M.MODE_WAVEFRONT if args.mode == "wavefront" else M.MODE_MEGAKERNEL
+    render_partial, sum_partials, stats = gpu_backend(ctx, s.camera, spp, w, h, mode=mode)
 
     def barrier():
         if world > 1:
@@ -184,13 +185,15 @@ def run_ours(args):
     if rank == 0:
         sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    integ_ms, render_ms, build_ms, rays = [], [], [], []
+    integ_ms, render_ms, build_ms, rays, trace_ms, trace_n, launches = [], [], [], [], [], [], 0
     ev0.record(stream)
     for _ in range(args.steps):
         del stats[:]
         step()
         st = stats[-1]
         integ_ms.append(st.integrate_ms); render_ms.append(st.render_ms); build_ms.append(st.build_ms); rays.append(st.rays)
+        trace_ms.append(st.trace_ms); trace_n.append(st.trace_launches)
+        launches += 7 + st.kernel_launches + 1     # build (3 ours + 4 CUB) + render_chunks' kernels + the final fixed-tree sum
     ev1.record(stream)
     barrier()
     ms_total = ev0.elapsed_time(ev1)
@@ -218,28 +221,37 @@ def run_ours(args):
         # algorithmic bytes of the dominant kernel: 64 B per node fetch + 48 B per triangle test, counted
         # by the COUNT variant on the same workload at reduced spp (per-ray averages are spp-independent)
         cspp = max(8, min(spp_per_gpu, 16))
-        ctx.render(s.camera, cspp, w, h, flags=M.FLAG_COUNT)
+        ctx.render(s.camera, cspp, w, h, mode=mode, flags=M.FLAG_COUNT)
         cs = ctx.last_stats
         bytes_per_ray = (64.0 * cs.node_visits + 48.0 * cs.tri_tests) / cs.rays
-        k_ms = sum(integ_ms) / len(integ_ms)
-        k_rays = rays[-1]
+        # dominant kernel: the megakernel (one launch per step), or wf_trace (one launch per wavefront iteration; its
+        # launches of a step are timed by one CUDA-event pair each and summed)
+        if args.mode == "wavefront":
+            kernel, n_k = "wf_trace", sum(trace_n) / len(trace_n)
+            k_ms_step = sum(trace_ms) / len(trace_ms)
+        else:
+            kernel, n_k = "pt_megakernel", 1
+            k_ms_step = sum(integ_ms) / len(integ_ms)
+        k_ms = k_ms_step / n_k                       # average launch duration
+        k_rays = rays[-1] / n_k                      # rays per launch
         achieved = bytes_per_ray * k_rays / (k_ms * 1e-3) / 1e9
         line = {
             "metric": "path-tracing throughput", "value": samples / ms_total * 1e-3, "unit": "Msamples/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "shipped scene (scenes/%s.obj)" % scene_name,
             "config": {"workload": args.workload, "scene": scene_name, "width": w, "height": h, "spp_total": spp,
-                       "spp_per_gpu": spp_per_gpu, "mode": "megakernel", "partition": "spp-split, 8 chunks, fixed-tree sum",
+                       "spp_per_gpu": spp_per_gpu, "mode": args.mode, "partition": "spp-split, 8 chunks, fixed-tree sum",
                        "l2_policy": "no flush: the scene (%.1f MB) is L2-resident by design; the timed kernel re-reads it "
                                     "billions of times per launch" % ((64 + 48 + 64) * s.n_faces / 1e6)},
             "mrays_per_s": rays_total / ms_total * 1e-3, "rays_per_sample": rays_total / samples,
             "lbvh_build_ms": sum(build_ms) / len(build_ms), "render_ms": sum(render_ms) / len(render_ms),
             "e2e": {"value": samples / e2e_ms * 1e-3, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": h * w * 3 * 4, "ms_per_step": e2e_ms / args.steps},
-            "gpu_launches": (7 + 3 + (1 if world > 1 else 1)) * args.steps,   # build 7 (3 ours + 4 CUB), raygen, integrator, chunk sum, final sum
+            "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
-                         "traffic": None, "peak_source": pk_src, "kernel": "pt_megakernel", "kernel_ms": k_ms,
+                         "traffic": None, "peak_source": pk_src, "kernel": kernel, "kernel_ms": k_ms, "launches_per_step": n_k,
+                         "kernel_ms_per_step": k_ms_step, "integrator_ms_per_step": sum(integ_ms) / len(integ_ms),
                          "bytes_per_ray": bytes_per_ray, "nodes_per_ray": cs.node_visits / cs.rays,
                          "tris_per_ray": cs.tri_tests / cs.rays,
                          "note": "algorithmic node+triangle bytes; the working set is L1/L2-resident so this is on-chip "
@@ -261,6 +273,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--mode", default="wavefront", choices=["wavefront", "megakernel"],
+                    help="integrator: wavefront (default, the faster one) or megakernel")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

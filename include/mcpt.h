@@ -97,7 +97,9 @@ typedef struct mcpt_stats {
     float render_ms;       /* CUDA-event time of the render kernels on the context's stream */
     float build_ms;        /* last mcpt_build_bvh */
     int32_t kernel_launches; /* kernels launched by the call (render: integrator + reduce) */
-    float integrate_ms;    /* CUDA-event time of the integrator kernel alone (the dominant kernel) */
+    float integrate_ms;    /* CUDA-event time of the integrator alone: the megakernel, or the whole wavefront loop */
+    float trace_ms;        /* wavefront mode: summed CUDA-event time of the wf_trace launches (the dominant kernel) */
+    int32_t trace_launches;/* wavefront mode: number of wf_trace launches (= loop iterations) */
 } mcpt_stats;
 
 enum { MCPT_MODE_MEGAKERNEL = 0, MCPT_MODE_WAVEFRONT = 1 };

@@ -27,6 +27,7 @@ struct mcpt_ctx {
     float* d_image = nullptr; size_t image_cap = 0;     // scratch: reduced image
     float* d_dirs = nullptr; size_t dirs_cap = 0;       // scratch: primary ray directions (K7)
     char* d_wf = nullptr; size_t wf_cap = 0;            // scratch: wavefront slot state + ray queue
+    std::vector<cudaEvent_t> trace_events; int wf_iterations = 0;   // event pair per wf_trace launch of the last render
     unsigned* h_alive = nullptr;                        // pinned: live-slot count read back by the wavefront loop
     void* d_io = nullptr; size_t io_cap = 0;            // scratch: rays in / hits out of mcpt_trace
     float last_build_ms = 0.f;
@@ -58,7 +59,7 @@ void free_scene(mcpt_ctx* c) {
     SceneBuffers& s = c->sb;
     cudaFree(s.pos); cudaFree(s.nrm); cudaFree(s.uv); cudaFree(s.mat_id); cudaFree(s.codes_obj); cudaFree(s.codes_sorted);
     cudaFree(s.iota); cudaFree(s.leaf_face); cudaFree(s.leaf_parent); cudaFree(s.flags); cudaFree(s.nodes); cudaFree(s.tri);
-    cudaFree(s.shade); cudaFree(s.root_box); cudaFree(s.cub_temp);
+    cudaFree(s.shade); cudaFree(s.root_box); cudaFree(s.cub_temp); cudaFree(s.qnodes); cudaFree(s.qgrid);
     s = SceneBuffers();
     cudaFree(c->d_materials); cudaFree(c->d_textures); cudaFree(c->d_tex_bytes); cudaFree(c->d_lights);
     cudaFree(c->d_light_tris); cudaFree(c->d_light_cdf);
@@ -78,7 +79,7 @@ DeviceScene device_scene(const mcpt_ctx* c) {
     DeviceScene d{};
     d.n_faces = c->sb.n_faces; d.n_materials = c->n_materials; d.n_textures = c->n_textures; d.n_lights = c->n_lights;
     d.root = 0; d.area0 = c->area0;
-    d.nodes = c->sb.nodes; d.tri = c->sb.tri; d.shade = c->sb.shade; d.leaf_face = c->sb.leaf_face; d.pos = c->sb.pos;
+    d.nodes = c->sb.nodes; d.qnodes = c->sb.qnodes; d.qgrid = c->sb.qgrid; d.tri = c->sb.tri; d.shade = c->sb.shade; d.leaf_face = c->sb.leaf_face; d.pos = c->sb.pos;
     d.materials = c->d_materials; d.textures = c->d_textures; d.tex_bytes = c->d_tex_bytes;
     d.lights = c->d_lights; d.light_tris = c->d_light_tris; d.light_cdf = c->d_light_cdf;
     return d;
@@ -117,6 +118,7 @@ MCPT_API void mcpt_destroy(mcpt_ctx* c) {
     cudaStreamSynchronize(c->stream);
     free_scene(c);
     cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); cudaFreeHost(c->h_alive);
+    for (cudaEvent_t ev : c->trace_events) cudaEventDestroy(ev);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->own_stream);
     delete c;
@@ -152,7 +154,7 @@ MCPT_API int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     CU(dev_alloc(s.pos, 9 * N)); CU(dev_alloc(s.nrm, 9 * N)); CU(dev_alloc(s.uv, 6 * N)); CU(dev_alloc(s.mat_id, N));
     CU(dev_alloc(s.codes_obj, N)); CU(dev_alloc(s.codes_sorted, N)); CU(dev_alloc(s.iota, N)); CU(dev_alloc(s.leaf_face, N));
     CU(dev_alloc(s.leaf_parent, N)); CU(dev_alloc(s.flags, N)); CU(dev_alloc(s.nodes, N)); CU(dev_alloc(s.tri, N));
-    CU(dev_alloc(s.shade, N)); CU(dev_alloc(s.root_box, 6));
+    CU(dev_alloc(s.shade, N)); CU(dev_alloc(s.root_box, 6)); CU(dev_alloc(s.qnodes, N)); CU(dev_alloc(s.qgrid, 1));
     s.cub_temp_bytes = lbvh_sort_temp_bytes(n);
     CU(cudaMalloc(&s.cub_temp, s.cub_temp_bytes ? s.cub_temp_bytes : 1));
     cudaStream_t st = c->stream;
@@ -268,6 +270,7 @@ void fill_stats(mcpt_ctx* c, mcpt_stats* st, double samples, const unsigned long
     if (!st) return;
     st->samples = samples; st->rays = (double)cnt[0]; st->node_visits = (double)cnt[1]; st->tri_tests = (double)cnt[2];
     st->render_ms = ms; st->build_ms = c->last_build_ms; st->kernel_launches = launches; st->integrate_ms = 0.f;
+    st->trace_ms = 0.f; st->trace_launches = 0;
 }
 // generateImg's camera basis (MTPC/pathTracing.cpp:276-294), in double on the host
 DCamera make_camera(const mcpt_camera* cam, int width, int height) {
@@ -302,6 +305,7 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
     const size_t plane = (size_t)width * height * 3;
     CU(grow(c->d_planes, c->planes_cap, sizeof(float) * plane * nch));
     CU(grow(c->d_dirs, c->dirs_cap, sizeof(float) * plane));
+    c->wf_iterations = 0;
     RenderParams P{};
     P.scene = device_scene(c);
     P.cam = make_camera(cam, width, height);
@@ -323,7 +327,7 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
         if (n_slots < 0) return fail_arg("render: image too large for one wavefront pass (more than 2^26 path slots)");
         if (c->n_lights > 32) return fail_arg("render: wavefront mode supports at most 32 lights");
         CU(grow(c->d_wf, c->wf_cap, wavefront_scratch_bytes(n_slots, c->n_lights)));
-        const int e = launch_wavefront(P, flags, c->d_wf, c->h_alive, c->stream, launches);
+        const int e = launch_wavefront(P, flags, c->d_wf, c->h_alive, c->stream, launches, &c->trace_events, &c->wf_iterations);
         if (e) return fail_cuda((cudaError_t)e, "wavefront loop");
     } else {
         const int e = launch_megakernel(P, flags, c->stream);
@@ -331,6 +335,19 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
         if (launches) *launches += 1;
     }
     CU(cudaEventRecord(c->ev2, c->stream));
+    return MCPT_OK;
+}
+// after the stream is synchronised: integrator time and, in wavefront mode, the summed wf_trace time
+int fill_kernel_times(mcpt_ctx* c, mcpt_stats* st) {
+    if (!st) return MCPT_OK;
+    CU(cudaEventElapsedTime(&st->integrate_ms, c->ev3, c->ev2));
+    double sum = 0;
+    for (int i = 0; i < c->wf_iterations; i++) {
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, c->trace_events[2 * i], c->trace_events[2 * i + 1]));
+        sum += ms;
+    }
+    st->trace_ms = (float)sum; st->trace_launches = c->wf_iterations;
     return MCPT_OK;
 }
 int check_render_args(mcpt_ctx* c, const mcpt_camera* cam, int& width, int& height, int spp) {
@@ -414,8 +431,7 @@ MCPT_API int mcpt_render_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, 
     CU(cudaMemcpy(cnt, c->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
     const long long s0 = (long long)cb * spp / MCPT_NUM_CHUNKS, s1 = (long long)ce * spp / MCPT_NUM_CHUNKS;
     fill_stats(c, st, (double)width * height * (double)(s1 - s0), cnt, ms, launches);
-    if (st) CU(cudaEventElapsedTime(&st->integrate_ms, c->ev3, c->ev2));
-    return MCPT_OK;
+    return fill_kernel_times(c, st);
 }
 
 MCPT_API int mcpt_render(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, int spp, int mode, int flags, float* rgb_out,
@@ -441,8 +457,7 @@ MCPT_API int mcpt_render(mcpt_ctx* c, const mcpt_camera* cam, int width, int hei
     unsigned long long cnt[4];
     CU(cudaMemcpy(cnt, c->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
     fill_stats(c, st, (double)width * height * (double)spp, cnt, ms, launches);
-    if (st) CU(cudaEventElapsedTime(&st->integrate_ms, c->ev3, c->ev2));
-    return MCPT_OK;
+    return fill_kernel_times(c, st);
 }
 
 }  // extern "C"

@@ -14,6 +14,14 @@ namespace mcpt {
 //   q[3] = (child0, child1, parent, unused) as int bits; child >= 0: internal node, child < 0: leaf ~child
 struct __align__(16) BvhNode { float4 q[4]; };
 
+// Traversal node, 32 B = 2 x uint4 (ONE 32-B sector per visit): the two child boxes on a 16-bit grid over the root box,
+//   c[s] = (lo.x | hi.x << 16, lo.y | hi.y << 16, lo.z | hi.z << 16, child index as in BvhNode)
+// lo rounded down and hi rounded up by two cells, so the quantised box contains the FP32 box with room for the
+// decode's rounding (DESIGN.md "quantised nodes").  Half the loads of BvhNode: traversal is bound by L1 wavefronts.
+struct __align__(16) QNode { uint4 c[2]; };
+// Grid of the quantisation, 8 floats: origin.xyz, 0, cell.xyz, 0  (world = origin + q * cell)
+struct __align__(16) QGrid { float4 origin, cell; };
+
 // Triangle, 48 B = 3 x float4, Morton-sorted leaf order: (v0, mat_id), (e1 = v1-v0, face_id), (e2 = v2-v0, 0)
 struct __align__(16) TriGeom { float4 v0m, e1f, e2; };
 
@@ -46,7 +54,9 @@ struct DeviceScene {
     int n_materials, n_textures, n_lights;
     int root;                 // >= 0 internal node, < 0 leaf (single-triangle scene)
     float area0;              // area of light 0: the frozen range of the selection uniform (quirk Q6)
-    const BvhNode* nodes;
+    const BvhNode* nodes;     // FP32 nodes (build product, structural tests)
+    const QNode* qnodes;      // 16-bit quantised nodes (what traversal reads)
+    const QGrid* qgrid;
     const TriGeom* tri;
     const TriShade* shade;
     const int* leaf_face;     // sorted leaf -> OBJ face index

@@ -157,6 +157,47 @@ __global__ void __launch_bounds__(256) emit_refit_kernel(int n, const double* __
     for (int a = 0; a < 3; a++) { root_box[a] = b.lo[a]; root_box[3 + a] = b.hi[a]; }
 }
 
+// ---- K4: quantise the refitted nodes onto a 16-bit grid over the root box ----------------------------------
+// One thread per internal node: 64-B FP32 node in, 32-B node out.  lo is floored and hi is ceiled, then both are
+// pushed out by two more cells: one for the float rounding of (x - origin) / cell here, one for the half-cell error of
+// the magic-number decode in node_step (trace.cuh).
+__device__ __forceinline__ unsigned quant_lo(float x, float o, float inv_cell) {
+    const float q = floorf((x - o) * inv_cell) - 2.0f;
+    return (unsigned)fminf(fmaxf(q, 0.0f), 65535.0f);
+}
+__device__ __forceinline__ unsigned quant_hi(float x, float o, float inv_cell) {
+    const float q = ceilf((x - o) * inv_cell) + 2.0f;
+    return (unsigned)fminf(fmaxf(q, 0.0f), 65535.0f);
+}
+__global__ void __launch_bounds__(256) quantize_nodes_kernel(int n_nodes, const BvhNode* __restrict__ nodes,
+                                                             const float* __restrict__ root_box, QNode* __restrict__ qnodes,
+                                                             QGrid* __restrict__ qgrid) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    float o[3], cell[3], inv[3];
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        const float lo = root_box[a], hi = root_box[3 + a];
+        const float ext = fmaxf(hi - lo, 1.0e-20f);
+        cell[a] = ext * (1.0f / 65520.0f);            // the root box spans cells 8 .. 65528: room for the outward push
+        o[a] = lo - 8.0f * cell[a];
+        inv[a] = 1.0f / cell[a];
+    }
+    if (i == 0) {
+        qgrid->origin = make_float4(o[0], o[1], o[2], 0.0f);
+        qgrid->cell = make_float4(cell[0], cell[1], cell[2], 0.0f);
+    }
+    const float4 q0 = nodes[i].q[0], q1 = nodes[i].q[1], q2 = nodes[i].q[2], q3 = nodes[i].q[3];
+    QNode out;
+    out.c[0] = make_uint4(quant_lo(q0.x, o[0], inv[0]) | (quant_hi(q0.y, o[0], inv[0]) << 16),
+                          quant_lo(q0.z, o[1], inv[1]) | (quant_hi(q0.w, o[1], inv[1]) << 16),
+                          quant_lo(q2.x, o[2], inv[2]) | (quant_hi(q2.y, o[2], inv[2]) << 16), __float_as_uint(q3.x));
+    out.c[1] = make_uint4(quant_lo(q1.x, o[0], inv[0]) | (quant_hi(q1.y, o[0], inv[0]) << 16),
+                          quant_lo(q1.z, o[1], inv[1]) | (quant_hi(q1.w, o[1], inv[1]) << 16),
+                          quant_lo(q2.z, o[2], inv[2]) | (quant_hi(q2.w, o[2], inv[2]) << 16), __float_as_uint(q3.y));
+    qnodes[i] = out;
+}
+
 // ---- host-side orchestration -----------------------------------------------------------------------
 size_t lbvh_sort_temp_bytes(int n) {
     size_t bytes = 0;
@@ -181,6 +222,8 @@ int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches) {
     }
     emit_refit_kernel<<<(n + tpb - 1) / tpb, tpb, 0, stream>>>(n, sb.pos, sb.nrm, sb.uv, sb.mat_id, sb.leaf_face, sb.leaf_parent,
                                                                sb.nodes, sb.flags, sb.tri, sb.shade, sb.root_box); nl++;
+    const int n_nodes = n > 1 ? n - 1 : 1;
+    quantize_nodes_kernel<<<(n_nodes + tpb - 1) / tpb, tpb, 0, stream>>>(n_nodes, sb.nodes, sb.root_box, sb.qnodes, sb.qgrid); nl++;
     if (launches) *launches = nl;
     sb.built = true;
     return (int)cudaGetLastError();

@@ -19,13 +19,15 @@ struct SceneBuffers {
     TriGeom* tri = nullptr;            // sorted order
     TriShade* shade = nullptr;         // sorted order
     float* root_box = nullptr;         // 6 floats: lo.xyz, hi.xyz
+    QNode* qnodes = nullptr;           // traversal nodes, same indexing as `nodes`
+    QGrid* qgrid = nullptr;
     void* cub_temp = nullptr; size_t cub_temp_bytes = 0;
     bool built = false;
 };
 
 // Bytes of CUB temp storage needed for n faces.
 size_t lbvh_sort_temp_bytes(int n);
-// K1 Morton -> CUB radix sort -> K2 radix tree -> K3 leaf emit + atomic bottom-up refit.
+// K1 Morton -> CUB radix sort -> K2 radix tree -> K3 leaf emit + atomic bottom-up refit -> K4 node quantisation.
 // Returns a cudaError_t as int; all work is enqueued on `stream`.
 int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches);
 

@@ -1,5 +1,6 @@
 // Launchers of the traversal / integrator / reduction kernels (render.cu).
 #pragma once
+#include <vector>
 #include "device_types.cuh"
 
 namespace mcpt {
@@ -14,7 +15,8 @@ int launch_megakernel(const RenderParams& P, int flags, cudaStream_t stream);
 // every few iterations to read the number of live path slots.
 int wavefront_slots(const RenderParams& P);                    // < 0: too many slots for the 26-bit ray id
 size_t wavefront_scratch_bytes(int n_slots, int n_lights);
-int launch_wavefront(const RenderParams& P, int flags, void* d_scratch, unsigned* h_alive_pinned, cudaStream_t stream, int* launches);
+int launch_wavefront(const RenderParams& P, int flags, void* d_scratch, unsigned* h_alive_pinned, cudaStream_t stream, int* launches,
+                     std::vector<cudaEvent_t>* trace_events, int* iterations);
 // K12: out[i] = scale * fixed pairwise tree sum over n planes (n in {1,2,4,8}).
 int launch_sum_planes(const float* d_planes, int n, long long count, float scale, float* d_out, cudaStream_t stream);
 }  // namespace mcpt

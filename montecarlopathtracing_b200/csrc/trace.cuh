@@ -24,73 +24,106 @@ struct Hit { float t, u, v; int k; };  // k = sorted-leaf index, -1 = miss
 // cracks; which of two edge-sharing triangles wins is then decided by t like in the reference.
 #define MCPT_EDGE_EPS 2.0e-6f
 
+// Per-ray constants.  Slab planes come from the 16-bit grid of the quantised nodes: a plane with grid coordinate q is
+// crossed at t = (origin + q*cell - o) / d = q*a + b with a = cell/d, b = (origin - o)/d.  q is turned into a float by
+// the magic-number trick — PRMT drops its 16 bits into the mantissa of 2^23, giving the float 2^23 + q exactly — so
+// t = (2^23 + q)*a + (b - 2^23*a): one PRMT and one FMA per plane.  b' = b - 2^23*a is rounded to half a grid cell
+// at worst, which the two-cell outward push of the quantiser covers (lbvh.cu K4).
+struct RayCtx { float3 o, d; float ax, ay, az, bx, by, bz; };
+
+__device__ __forceinline__ RayCtx ray_setup(const float3 o, const float3 d, const QGrid* __restrict__ grid) {
+    RayCtx r; r.o = o; r.d = d;
+    const float4 go = __ldg(&grid->origin), gc = __ldg(&grid->cell);
+    const float ooeps = 1.0e-24f;  // avoid inf/NaN slabs for axis-parallel rays
+    const float idx = 1.0f / (fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+    const float idy = 1.0f / (fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+    const float idz = 1.0f / (fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+    r.ax = gc.x * idx; r.ay = gc.y * idy; r.az = gc.z * idz;
+    r.bx = fmaf(-8388608.0f, r.ax, (go.x - o.x) * idx);
+    r.by = fmaf(-8388608.0f, r.ay, (go.y - o.y) * idy);
+    r.bz = fmaf(-8388608.0f, r.az, (go.z - o.z) * idz);
+    return r;
+}
+
+// Stack bottom: negative like a leaf, never a valid ~k.
+#define MCPT_SENT ((int)0x80000000)
+
+__device__ __forceinline__ float q_lo(unsigned w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7410)); }
+__device__ __forceinline__ float q_hi(unsigned w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7432)); }
+
+// One internal-node step: fetch the 32-B node (two 16-B loads, one sector), slab-test both children against
+// [0, best_t], descend into the nearer hit child (pushing the farther) or pop.  `node` >= 0 on entry.
+template <bool COUNT>
+__device__ __forceinline__ void node_step(const QNode* __restrict__ nodes, int& node, const RayCtx& r, const float best_t,
+                                          int* stack, int& sp, unsigned& n_nodes) {
+    const uint4 k0 = __ldg(&nodes[node].c[0]);
+    const uint4 k1 = __ldg(&nodes[node].c[1]);
+    if (COUNT) n_nodes++;
+    const float a0 = fmaf(q_lo(k0.x), r.ax, r.bx), b0 = fmaf(q_hi(k0.x), r.ax, r.bx);
+    const float a1 = fmaf(q_lo(k0.y), r.ay, r.by), b1 = fmaf(q_hi(k0.y), r.ay, r.by);
+    const float a2 = fmaf(q_lo(k0.z), r.az, r.bz), b2 = fmaf(q_hi(k0.z), r.az, r.bz);
+    const float c0min = fmaxf(fmaxf(fminf(a0, b0), fminf(a1, b1)), fmaxf(fminf(a2, b2), 0.0f));
+    const float c0max = fminf(fminf(fmaxf(a0, b0), fmaxf(a1, b1)), fminf(fmaxf(a2, b2), best_t));
+    const float e0 = fmaf(q_lo(k1.x), r.ax, r.bx), f0 = fmaf(q_hi(k1.x), r.ax, r.bx);
+    const float e1 = fmaf(q_lo(k1.y), r.ay, r.by), f1 = fmaf(q_hi(k1.y), r.ay, r.by);
+    const float e2 = fmaf(q_lo(k1.z), r.az, r.bz), f2 = fmaf(q_hi(k1.z), r.az, r.bz);
+    const float c1min = fmaxf(fmaxf(fminf(e0, f0), fminf(e1, f1)), fmaxf(fminf(e2, f2), 0.0f));
+    const float c1max = fminf(fminf(fmaxf(e0, f0), fmaxf(e1, f1)), fminf(fmaxf(e2, f2), best_t));
+    const bool h0 = c0min <= c0max, h1 = c1min <= c1max;
+    const int c0 = (int)k0.w, c1 = (int)k1.w;
+    if (h0 && h1) {
+        const bool swap = c1min < c0min;   // near child first
+        node = swap ? c1 : c0;
+        if (sp < MCPT_STACK_SIZE) stack[sp++] = swap ? c0 : c1;
+    } else if (h0 || h1) {
+        node = h0 ? c0 : c1;
+    } else {
+        node = stack[--sp];
+    }
+}
+
+// One leaf step: Möller–Trumbore on triangle ~node, keep it if it beats `best`, then pop.
+template <bool COUNT>
+__device__ __forceinline__ void leaf_step(const TriGeom* __restrict__ tris, int& node, const RayCtx& r, Hit& best, int* stack,
+                                          int& sp, unsigned& n_tris) {
+    const int k = ~node;
+    const float4 v0 = __ldg(&tris[k].v0m);
+    const float4 e1 = __ldg(&tris[k].e1f);
+    const float4 e2 = __ldg(&tris[k].e2);
+    if (COUNT) n_tris++;
+    const float3 E1 = f3(e1), E2 = f3(e2);
+    const float3 pvec = cross(r.d, E2);
+    const float inv_det = 1.0f / dot(E1, pvec);  // det == 0 -> inf/NaN -> every comparison below fails
+    const float3 tvec = r.o - f3(v0);
+    const float u = dot(tvec, pvec) * inv_det;
+    const float3 qvec = cross(tvec, E1);
+    const float v = dot(r.d, qvec) * inv_det;
+    const float t = dot(E2, qvec) * inv_det;
+    if (u >= -MCPT_EDGE_EPS && v >= -MCPT_EDGE_EPS && u + v <= 1.0f + MCPT_EDGE_EPS && t > 0.0f && (t < best.t || (t == best.t && k < best.k))) {
+        // quirk Q2 in full: the reference keeps a hit only if t = (p.x - o.x)/d.x > 0 with p.x = o.x + d.x*t formed in
+        // FP64 (MTPC/pathTracing.cpp:347,355); when |d.x*t| is below half an ulp of o.x that is 0 and the hit is
+        // dropped.  Candidates that pass the FP32 test are rare (1-2 per ray), so the FP64 check is cheap.
+        if (__dadd_rn((double)r.o.x, __dmul_rn((double)r.d.x, (double)t)) != (double)r.o.x) {
+            best.t = t; best.u = u; best.v = v; best.k = k;
+        }
+    }
+    node = stack[--sp];
+}
+
+// Closest hit of one ray, one ray per thread from start to finish (megakernel and the batch kernel of seam 2).
 template <bool COUNT>
 __device__ __forceinline__ Hit trace_closest(const DeviceScene& sc, const float3 o, const float3 d, const float tmax,
                                              unsigned& n_nodes, unsigned& n_tris) {
     Hit best; best.t = tmax; best.u = 0.f; best.v = 0.f; best.k = -1;
     if (d.x == 0.0f) return best;
-    const float ooeps = 1.0e-24f;  // avoid inf/NaN slabs for axis-parallel rays
-    const float idx = 1.0f / (fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
-    const float idy = 1.0f / (fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
-    const float idz = 1.0f / (fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
-    const float oodx = o.x * idx, oody = o.y * idy, oodz = o.z * idz;
-    const BvhNode* __restrict__ nodes = sc.nodes;
-    const TriGeom* __restrict__ tris = sc.tri;
+    const RayCtx r = ray_setup(o, d, sc.qgrid);
     int stack[MCPT_STACK_SIZE];
-    int sp = 0;
+    stack[0] = MCPT_SENT;
+    int sp = 1;
     int node = sc.root;
-    while (true) {
-        if (node >= 0) {
-            const float4 n0 = __ldg(&nodes[node].q[0]);
-            const float4 n1 = __ldg(&nodes[node].q[1]);
-            const float4 nz = __ldg(&nodes[node].q[2]);
-            const float4 cq = __ldg(&nodes[node].q[3]);
-            if (COUNT) n_nodes++;
-            const float a0 = fmaf(n0.x, idx, -oodx), b0 = fmaf(n0.y, idx, -oodx);
-            const float a1 = fmaf(n0.z, idy, -oody), b1 = fmaf(n0.w, idy, -oody);
-            const float a2 = fmaf(nz.x, idz, -oodz), b2 = fmaf(nz.y, idz, -oodz);
-            const float c0min = fmaxf(fmaxf(fminf(a0, b0), fminf(a1, b1)), fmaxf(fminf(a2, b2), 0.0f));
-            const float c0max = fminf(fminf(fmaxf(a0, b0), fmaxf(a1, b1)), fminf(fmaxf(a2, b2), best.t));
-            const float e0 = fmaf(n1.x, idx, -oodx), f0 = fmaf(n1.y, idx, -oodx);
-            const float e1 = fmaf(n1.z, idy, -oody), f1 = fmaf(n1.w, idy, -oody);
-            const float e2 = fmaf(nz.z, idz, -oodz), f2 = fmaf(nz.w, idz, -oodz);
-            const float c1min = fmaxf(fmaxf(fminf(e0, f0), fminf(e1, f1)), fmaxf(fminf(e2, f2), 0.0f));
-            const float c1max = fminf(fminf(fmaxf(e0, f0), fmaxf(e1, f1)), fminf(fmaxf(e2, f2), best.t));
-            const bool h0 = c0min <= c0max, h1 = c1min <= c1max;
-            const int c0 = __float_as_int(cq.x), c1 = __float_as_int(cq.y);
-            if (h0 && h1) {
-                const bool swap = c1min < c0min;
-                node = swap ? c1 : c0;
-                if (sp < MCPT_STACK_SIZE) stack[sp++] = swap ? c0 : c1;
-                continue;
-            }
-            if (h0) { node = c0; continue; }
-            if (h1) { node = c1; continue; }
-        } else {
-            const int k = ~node;
-            const float4 v0 = __ldg(&tris[k].v0m);
-            const float4 e1 = __ldg(&tris[k].e1f);
-            const float4 e2 = __ldg(&tris[k].e2);
-            if (COUNT) n_tris++;
-            const float3 E1 = f3(e1), E2 = f3(e2);
-            const float3 pvec = cross(d, E2);
-            const float inv_det = 1.0f / dot(E1, pvec);  // det == 0 -> inf/NaN -> every comparison below fails
-            const float3 tvec = o - f3(v0);
-            const float u = dot(tvec, pvec) * inv_det;
-            const float3 qvec = cross(tvec, E1);
-            const float v = dot(d, qvec) * inv_det;
-            const float t = dot(E2, qvec) * inv_det;
-            if (u >= -MCPT_EDGE_EPS && v >= -MCPT_EDGE_EPS && u + v <= 1.0f + MCPT_EDGE_EPS && t > 0.0f && (t < best.t || (t == best.t && k < best.k))) {
-                // quirk Q2 in full: the reference keeps a hit only if t = (p.x - o.x)/d.x > 0 with p.x = o.x + d.x*t formed
-                // in FP64 (MTPC/pathTracing.cpp:347,355); when |d.x*t| is below half an ulp of o.x that is 0 and the
-                // hit is dropped.  Candidates that pass the FP32 test are rare (1-2 per ray), so the FP64 check is cheap.
-                if (__dadd_rn((double)o.x, __dmul_rn((double)d.x, (double)t)) != (double)o.x) {
-                    best.t = t; best.u = u; best.v = v; best.k = k;
-                }
-            }
-        }
-        if (sp == 0) break;
-        node = stack[--sp];
+    while (node != MCPT_SENT) {
+        if (node >= 0) node_step<COUNT>(sc.qnodes, node, r, best.t, stack, sp, n_nodes);
+        else leaf_step<COUNT>(sc.tri, node, r, best, stack, sp, n_tris);
     }
     return best;
 }

@@ -15,6 +15,8 @@
 //
 // HBM layout (SoA over n_slots; every field a 16-B vector): hit, hit0, sum_s, beta_m, L, rd, pend[n_lights][n_slots];
 // vis[n_slots]; ray queue ray_o / ray_d of (n_lights + 1) * n_slots entries.
+#include <cstdlib>
+#include <vector>
 #include "render.h"
 #include "shade.cuh"
 
@@ -222,34 +224,72 @@ __global__ void __launch_bounds__(256) wf_shade(const RenderParams P, const WfBu
 }
 
 // ---- K9: trace the queue -----------------------------------------------------------------------------------
-// Persistent warps fetch 32 rays at a time from the queue head (one atomic per warp), so a warp that drew short
-// rays goes back for more instead of idling behind a long one.
+// Persistent warps with per-LANE ray replacement.  Ray lengths are heavy-tailed (a ray that grazes the 15k-triangle
+// table visits ten times the nodes of one that hits a wall), so a warp that traces 32 rays to completion idles most
+// of its lanes behind the longest ray (ncu: 4.7-6.3 of 32 lanes active).  Here a lane whose ray is finished parks
+// its result and, once `refill_min` lanes are parked, the parked lanes write their results back and pull new rays
+// from the queue head with one atomic for the warp.  Every loop iteration is one traversal step per lane: lanes at
+// an internal node take a node step; lanes at a leaf take a leaf step once `leaf_min` lanes have gathered there (or
+// no lane is at a node), so the triangle test is not issued for one or two lanes at a time.
 template <bool COUNT>
-__global__ void __launch_bounds__(128) wf_trace(const DeviceScene sc, const WfBuffers B, const int iter, unsigned long long* stats) {
+__global__ void __launch_bounds__(128) wf_trace(const DeviceScene sc, const WfBuffers B, const int iter, unsigned long long* stats,
+                                                const int refill_min, const int leaf_min) {
     const int par = iter & 1;
     const unsigned n = __ldcg(B.counters + WFC_TAIL + par);
     unsigned* head = B.counters + WFC_HEAD + par;
     const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
     unsigned n_nodes = 0, n_tris = 0;
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[0], (unsigned long long)n);
+    RayCtx r = ray_setup(f3(0.f, 0.f, 0.f), f3(1.f, 1.f, 1.f), sc.qgrid);
+    Hit best; best.t = 0.f; best.u = 0.f; best.v = 0.f; best.k = -1;
+    int stack[MCPT_STACK_SIZE];
+    stack[0] = MCPT_SENT;
+    int sp = 1, node = MCPT_SENT;
+    unsigned id = 0;
+    bool has_ray = false, exhausted = false;
+    auto write_back = [&]() {
+        const unsigned slot = id & ((1u << WF_ID_BITS) - 1u), kind = id >> WF_ID_BITS;
+        if (kind == 0u) {
+            __stcg(&B.hit[slot], make_float4(best.t, best.u, best.v, __int_as_float(best.k)));
+        } else if (best.k >= 0 && __float_as_int(__ldg(&sc.tri[best.k].v0m).w) == sc.lights[kind - 1].mat_id) {
+            atomicOr(&B.vis[slot], 1u << (kind - 1));   // visible iff the CLOSEST hit carries the light's material (:212-215)
+        }
+    };
     while (true) {
-        unsigned base = 0;
-        if (lane == 0) base = atomicAdd(head, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        const unsigned i = base + lane;
-        if (i < n) {
-            const float4 o4 = __ldcg(&B.ray_o[i]), d4 = __ldcg(&B.ray_d[i]);
-            const unsigned id = __float_as_uint(d4.w);
-            const unsigned slot = id & ((1u << WF_ID_BITS) - 1u), kind = id >> WF_ID_BITS;
-            const Hit h = trace_closest<COUNT>(sc, f3(o4), f3(d4), o4.w, n_nodes, n_tris);
-            if (kind == 0u) {
-                __stcg(&B.hit[slot], make_float4(h.t, h.u, h.v, __int_as_float(h.k)));
-            } else if (h.k >= 0 && __float_as_int(__ldg(&sc.tri[h.k].v0m).w) == sc.lights[kind - 1].mat_id) {
-                atomicOr(&B.vis[slot], 1u << (kind - 1));   // visible iff the CLOSEST hit carries the light's material (:212-215)
+        const bool idle = node == MCPT_SENT;
+        const unsigned im = __ballot_sync(0xffffffffu, idle);
+        if (im != 0u) {
+            if (exhausted) {
+                if (im == 0xffffffffu) break;
+            } else if (__popc(im) >= refill_min || im == 0xffffffffu) {
+                if (idle && has_ray) { write_back(); has_ray = false; }
+                const int leader = __ffs(im) - 1;
+                unsigned base = 0;
+                if (lane == leader) base = atomicAdd(head, (unsigned)__popc(im));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (idle) {
+                    const unsigned i = base + __popc(im & lt_mask);
+                    if (i < n) {
+                        const float4 o4 = __ldcg(&B.ray_o[i]), d4 = __ldcg(&B.ray_d[i]);
+                        id = __float_as_uint(d4.w);
+                        r = ray_setup(f3(o4), f3(d4), sc.qgrid);
+                        best.t = o4.w; best.u = 0.f; best.v = 0.f; best.k = -1;
+                        sp = 1; has_ray = true;
+                        node = (d4.x == 0.0f) ? MCPT_SENT : sc.root;   // quirk Q2: d.x == 0 hits nothing
+                    }
+                }
+                if (base + (unsigned)__popc(im) >= n) exhausted = true;
+                continue;
             }
         }
+        const bool at_node = node >= 0;
+        const bool at_leaf = !at_node && !idle;
+        const unsigned nm = __ballot_sync(0xffffffffu, at_node), lm = __ballot_sync(0xffffffffu, at_leaf);
+        if (at_node) node_step<COUNT>(sc.qnodes, node, r, best.t, stack, sp, n_nodes);
+        if (at_leaf && (__popc(lm) >= leaf_min || nm == 0u)) leaf_step<COUNT>(sc.tri, node, r, best, stack, sp, n_tris);
     }
+    if (has_ray) write_back();
     if (COUNT) {
         const unsigned a = __reduce_add_sync(0xffffffffu, n_nodes), b = __reduce_add_sync(0xffffffffu, n_tris);
         if (lane == 0) { atomicAdd(&stats[1], (unsigned long long)a); atomicAdd(&stats[2], (unsigned long long)b); }
@@ -258,6 +298,8 @@ __global__ void __launch_bounds__(128) wf_trace(const DeviceScene sc, const WfBu
 
 // ---- host side ----------------------------------------------------------------------------------------------
 static size_t align256(size_t b) { return (b + 255) & ~(size_t)255; }
+// developer tuning knobs (defaults are the measured best); read once per render
+static int env_int(const char* name, int dflt) { const char* v = getenv(name); return v && *v ? atoi(v) : dflt; }
 
 int wavefront_slots(const RenderParams& P) {
     const long long n_tiles = (long long)((P.cam.width + 7) / 8) * ((P.cam.height + 3) / 4);
@@ -272,7 +314,8 @@ size_t wavefront_scratch_bytes(int n_slots, int n_lights) {
 }
 
 // Runs the shade/trace loop until every slot is done.  h_alive: pinned host word for the termination check.
-int launch_wavefront(const RenderParams& P, int flags, void* scratch, unsigned* h_alive, cudaStream_t stream, int* launches) {
+int launch_wavefront(const RenderParams& P, int flags, void* scratch, unsigned* h_alive, cudaStream_t stream, int* launches,
+                     std::vector<cudaEvent_t>* trace_events, int* iterations) {
     const int n_slots = wavefront_slots(P);
     const int nl = P.scene.n_lights;
     if (n_slots <= 0 || nl > WF_MAX_LIGHTS) return (int)cudaErrorInvalidConfiguration;
@@ -291,15 +334,26 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, unsigned* 
     if (e != cudaSuccess) return (int)e;
     const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
     const int shade_blocks = (n_slots + 255) / 256;
-    const int trace_blocks = 148 * 16;   // 16 CTAs of 4 warps per SM
+    const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 16);   // CTAs of 4 warps
+    const int refill_min = env_int("MCPT_REFILL_MIN", 8), leaf_min = env_int("MCPT_LEAF_MIN", 1);
     int nlaunch = 0;
     const int batch = 8;
     for (int iter = 0;; iter++) {
         if (reuse) wf_shade<true><<<shade_blocks, 256, 0, stream>>>(P, B, iter);
         else wf_shade<false><<<shade_blocks, 256, 0, stream>>>(P, B, iter);
-        if (count) wf_trace<true><<<trace_blocks, 128, 0, stream>>>(P.scene, B, iter, P.counters);
-        else wf_trace<false><<<trace_blocks, 128, 0, stream>>>(P.scene, B, iter, P.counters);
+        if (trace_events) {   // one event pair per wf_trace launch; the pool grows and is reused across renders
+            while (trace_events->size() < 2 * (size_t)(iter + 1)) {
+                cudaEvent_t ev; e = cudaEventCreate(&ev);
+                if (e != cudaSuccess) return (int)e;
+                trace_events->push_back(ev);
+            }
+            cudaEventRecord((*trace_events)[2 * iter], stream);
+        }
+        if (count) wf_trace<true><<<trace_blocks, 128, 0, stream>>>(P.scene, B, iter, P.counters, refill_min, leaf_min);
+        else wf_trace<false><<<trace_blocks, 128, 0, stream>>>(P.scene, B, iter, P.counters, refill_min, leaf_min);
+        if (trace_events) cudaEventRecord((*trace_events)[2 * iter + 1], stream);
         nlaunch += 2;
+        if (iterations) *iterations = iter + 1;
         if (iter % batch == batch - 1) {
             e = cudaMemcpyAsync(h_alive, B.counters + WFC_ALIVE + (iter & 1), 4, cudaMemcpyDeviceToHost, stream);
             if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
