@@ -218,12 +218,12 @@ def run_ours(args):
         pk, pk_src = peaks()
         samples = float(w) * h * spp * args.steps
         ms_step = ms_total / args.steps
-        # algorithmic bytes of the dominant kernel: 64 B per node fetch + 48 B per triangle test, counted
+        # algorithmic bytes of the dominant kernel: 32 B per node fetch + 48 B per triangle test, counted
         # by the COUNT variant on the same workload at reduced spp (per-ray averages are spp-independent)
         cspp = max(8, min(spp_per_gpu, 16))
         ctx.render(s.camera, cspp, w, h, mode=mode, flags=M.FLAG_COUNT)
         cs = ctx.last_stats
-        bytes_per_ray = (64.0 * cs.node_visits + 48.0 * cs.tri_tests) / cs.rays
+        bytes_per_ray = (32.0 * cs.node_visits + 48.0 * cs.tri_tests) / cs.rays
         # dominant kernel: the megakernel (one launch per step), or wf_trace (one launch per wavefront iteration; its
         # launches of a step are timed by one CUDA-event pair each and summed)
         if args.mode == "wavefront":
@@ -241,8 +241,9 @@ def run_ours(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "shipped scene (scenes/%s.obj)" % scene_name,
             "config": {"workload": args.workload, "scene": scene_name, "width": w, "height": h, "spp_total": spp,
                        "spp_per_gpu": spp_per_gpu, "mode": args.mode, "partition": "spp-split, 8 chunks, fixed-tree sum",
-                       "l2_policy": "no flush: the scene (%.1f MB) is L2-resident by design; the timed kernel re-reads it "
-                                    "billions of times per launch" % ((64 + 48 + 64) * s.n_faces / 1e6)},
+                       "l2_policy": "no flush: the scene (%.1f MB of nodes+triangles) is L1/L2-resident by design and every "
+                                    "launch re-reads it millions of times; the wavefront state and ray queues (~%d MB) "
+                                    "exceed L2 at this size" % ((32 + 48 + 64) * s.n_faces / 1e6, int(w * h * (100 + 16 * len(s.lights) + 32 * (len(s.lights) + 1)) / 1e6))},
             "mrays_per_s": rays_total / ms_total * 1e-3, "rays_per_sample": rays_total / samples,
             "lbvh_build_ms": sum(build_ms) / len(build_ms), "render_ms": sum(render_ms) / len(render_ms),
             "e2e": {"value": samples / e2e_ms * 1e-3, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,

@@ -27,8 +27,7 @@ struct mcpt_ctx {
     float* d_image = nullptr; size_t image_cap = 0;     // scratch: reduced image
     float* d_dirs = nullptr; size_t dirs_cap = 0;       // scratch: primary ray directions (K7)
     char* d_wf = nullptr; size_t wf_cap = 0;            // scratch: wavefront slot state + ray queue
-    std::vector<cudaEvent_t> trace_events; int wf_iterations = 0;   // event pair per wf_trace launch of the last render
-    unsigned* h_alive = nullptr;                        // pinned: live-slot count read back by the wavefront loop
+    WfHost wfh;                                         // streams/events of the wavefront loop
     void* d_io = nullptr; size_t io_cap = 0;            // scratch: rays in / hits out of mcpt_trace
     float last_build_ms = 0.f;
     bool scene_loaded = false;
@@ -107,7 +106,6 @@ MCPT_API int mcpt_create(int device, mcpt_ctx** out) {
     c->stream = c->own_stream;
     CU(cudaEventCreate(&c->ev0)); CU(cudaEventCreate(&c->ev1)); CU(cudaEventCreate(&c->ev2)); CU(cudaEventCreate(&c->ev3));
     CU(dev_alloc(c->d_counters, 4));
-    CU(cudaHostAlloc((void**)&c->h_alive, sizeof(unsigned), cudaHostAllocDefault));
     *out = c;
     return MCPT_OK;
 }
@@ -117,8 +115,7 @@ MCPT_API void mcpt_destroy(mcpt_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     free_scene(c);
-    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); cudaFreeHost(c->h_alive);
-    for (cudaEvent_t ev : c->trace_events) cudaEventDestroy(ev);
+    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); c->wfh.destroy();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->own_stream);
     delete c;
@@ -305,7 +302,7 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
     const size_t plane = (size_t)width * height * 3;
     CU(grow(c->d_planes, c->planes_cap, sizeof(float) * plane * nch));
     CU(grow(c->d_dirs, c->dirs_cap, sizeof(float) * plane));
-    c->wf_iterations = 0;
+    c->wfh.iterations = 0;
     RenderParams P{};
     P.scene = device_scene(c);
     P.cam = make_camera(cam, width, height);
@@ -327,7 +324,7 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
         if (n_slots < 0) return fail_arg("render: image too large for one wavefront pass (more than 2^26 path slots)");
         if (c->n_lights > 32) return fail_arg("render: wavefront mode supports at most 32 lights");
         CU(grow(c->d_wf, c->wf_cap, wavefront_scratch_bytes(n_slots, c->n_lights)));
-        const int e = launch_wavefront(P, flags, c->d_wf, c->h_alive, c->stream, launches, &c->trace_events, &c->wf_iterations);
+        const int e = launch_wavefront(P, flags, c->d_wf, c->wfh, c->stream, launches);
         if (e) return fail_cuda((cudaError_t)e, "wavefront loop");
     } else {
         const int e = launch_megakernel(P, flags, c->stream);
@@ -342,12 +339,12 @@ int fill_kernel_times(mcpt_ctx* c, mcpt_stats* st) {
     if (!st) return MCPT_OK;
     CU(cudaEventElapsedTime(&st->integrate_ms, c->ev3, c->ev2));
     double sum = 0;
-    for (int i = 0; i < c->wf_iterations; i++) {
+    for (int i = 0; i < c->wfh.iterations; i++) {
         float ms = 0.f;
-        CU(cudaEventElapsedTime(&ms, c->trace_events[2 * i], c->trace_events[2 * i + 1]));
+        CU(cudaEventElapsedTime(&ms, c->wfh.trace_events[2 * i], c->wfh.trace_events[2 * i + 1]));
         sum += ms;
     }
-    st->trace_ms = (float)sum; st->trace_launches = c->wf_iterations;
+    st->trace_ms = (float)sum; st->trace_launches = c->wfh.iterations;
     return MCPT_OK;
 }
 int check_render_args(mcpt_ctx* c, const mcpt_camera* cam, int& width, int& height, int spp) {

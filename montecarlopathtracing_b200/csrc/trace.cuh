@@ -82,11 +82,9 @@ __device__ __forceinline__ void node_step(const QNode* __restrict__ nodes, int& 
     }
 }
 
-// One leaf step: Möller–Trumbore on triangle ~node, keep it if it beats `best`, then pop.
+// Möller–Trumbore on sorted triangle k; keeps it in `best` if it is the closer hit (ties: lower leaf index).
 template <bool COUNT>
-__device__ __forceinline__ void leaf_step(const TriGeom* __restrict__ tris, int& node, const RayCtx& r, Hit& best, int* stack,
-                                          int& sp, unsigned& n_tris) {
-    const int k = ~node;
+__device__ __forceinline__ void tri_test(const TriGeom* __restrict__ tris, const int k, const RayCtx& r, Hit& best, unsigned& n_tris) {
     const float4 v0 = __ldg(&tris[k].v0m);
     const float4 e1 = __ldg(&tris[k].e1f);
     const float4 e2 = __ldg(&tris[k].e2);
@@ -107,6 +105,13 @@ __device__ __forceinline__ void leaf_step(const TriGeom* __restrict__ tris, int&
             best.t = t; best.u = u; best.v = v; best.k = k;
         }
     }
+}
+
+// One leaf step: test triangle ~node, then pop.
+template <bool COUNT>
+__device__ __forceinline__ void leaf_step(const TriGeom* __restrict__ tris, int& node, const RayCtx& r, Hit& best, int* stack,
+                                          int& sp, unsigned& n_tris) {
+    tri_test<COUNT>(tris, ~node, r, best, n_tris);
     node = stack[--sp];
 }
 

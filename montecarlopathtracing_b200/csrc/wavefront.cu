@@ -23,7 +23,7 @@
 namespace mcpt {
 
 enum { WF_NEW = 0, WF_WAIT_PRIMARY = 1, WF_WAIT_VERTEX = 2, WF_DONE = 3 };
-enum { WF_ID_BITS = 26, WF_MAX_LIGHTS = 32 };
+enum { WF_ID_BITS = 26, WF_MAX_LIGHTS = 32 };   // WF_MAX_PIPES is in render.h
 // counters (unsigned, in the scratch block): [0,1] queue tail by iteration parity, [2,3] slots alive by parity,
 // [4,5] queue head (dynamic fetch) by parity
 enum { WFC_TAIL = 0, WFC_ALIVE = 2, WFC_HEAD = 4, WFC_COUNT = 8 };
@@ -40,7 +40,8 @@ struct WfBuffers {
     float4* ray_o;   // queue: origin, tmax
     float4* ray_d;   // queue: direction, id = slot | (kind << 26), kind 0 = primary/extend, l+1 = shadow ray of light l
     unsigned* counters;
-    int n_slots;
+    int n_slots;               // all slots (stride of pend[])
+    int slot_begin, slot_end;  // the slots of this pipe
 };
 
 // meta: state(2) | lobe(2) << 2 | has_extend << 4 | have_hit0 << 5 | bounce << 8 | chunk << 16
@@ -70,17 +71,17 @@ __global__ void __launch_bounds__(256) wf_shade(const RenderParams P, const WfBu
     const DeviceScene& sc = P.scene;
     const int W = P.cam.width, H = P.cam.height;
     const int tiles_x = (W + 7) >> 3, tiles_y = (H + 3) >> 2, n_tiles = tiles_x * tiles_y;
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;      // the grid covers whole warps
+    const int slot = B.slot_begin + blockIdx.x * blockDim.x + threadIdx.x;      // the grid covers whole warps
     const int par = iter & 1;
     unsigned* tail = B.counters + WFC_TAIL + par;
-    if (slot == 0) {   // the other parity's counters were last used by iteration iter-1, which has completed
+    if (slot == B.slot_begin) {   // the other parity's counters were last used by iteration iter-1, which has completed
         B.counters[WFC_TAIL + (par ^ 1)] = 0u; B.counters[WFC_ALIVE + (par ^ 1)] = 0u; B.counters[WFC_HEAD + (par ^ 1)] = 0u;
     }
     const int lane = threadIdx.x & 31;
     const int warp_id = slot >> 5;
     const int group = warp_id / n_tiles, tile = warp_id % n_tiles;
     const int x = (tile % tiles_x) * 8 + (lane & 7), y = (tile / tiles_x) * 4 + (lane >> 3);
-    const bool valid = slot < B.n_slots && x < W && y < H;
+    const bool valid = slot < B.slot_end && x < W && y < H;
     const unsigned pixel = (unsigned)(y * W + x);
     const int nl = sc.n_lights;
 
@@ -216,7 +217,7 @@ __global__ void __launch_bounds__(256) wf_shade(const RenderParams P, const WfBu
             if (store_hit0) __stcg(&B.hit0[slot], make_float4(hit0.t, hit0.u, hit0.v, __int_as_float(hit0.k)));
         }
         (void)was_done_before;
-    } else if (slot < B.n_slots && iter == 0) {
+    } else if (slot < B.slot_end && iter == 0) {
         __stcg(&B.beta_m[slot], make_float4(0.f, 0.f, 0.f, __uint_as_float(pack_meta(WF_DONE, 0, false, false, 0, 0))));
     }
     const unsigned alive = __ballot_sync(0xffffffffu, valid && state != WF_DONE);
@@ -233,7 +234,8 @@ __global__ void __launch_bounds__(256) wf_shade(const RenderParams P, const WfBu
 // no lane is at a node), so the triangle test is not issued for one or two lanes at a time.
 template <bool COUNT>
 __global__ void __launch_bounds__(128) wf_trace(const DeviceScene sc, const WfBuffers B, const int iter, unsigned long long* stats,
-                                                const int refill_min, const int leaf_min) {
+                                                const int refill_min, const int leaf_min, const int block_min,
+                                                const int node_steps) {
     const int par = iter & 1;
     const unsigned n = __ldcg(B.counters + WFC_TAIL + par);
     unsigned* head = B.counters + WFC_HEAD + par;
@@ -256,8 +258,9 @@ __global__ void __launch_bounds__(128) wf_trace(const DeviceScene sc, const WfBu
             atomicOr(&B.vis[slot], 1u << (kind - 1));   // visible iff the CLOSEST hit carries the light's material (:212-215)
         }
     };
+    int pend = 0;   // postponed leaf (negative ~k), 0 = none
     while (true) {
-        const bool idle = node == MCPT_SENT;
+        const bool idle = node == MCPT_SENT && pend == 0;
         const unsigned im = __ballot_sync(0xffffffffu, idle);
         if (im != 0u) {
             if (exhausted) {
@@ -283,11 +286,19 @@ __global__ void __launch_bounds__(128) wf_trace(const DeviceScene sc, const WfBu
                 continue;
             }
         }
-        const bool at_node = node >= 0;
-        const bool at_leaf = !at_node && !idle;
-        const unsigned nm = __ballot_sync(0xffffffffu, at_node), lm = __ballot_sync(0xffffffffu, at_leaf);
-        if (at_node) node_step<COUNT>(sc.qnodes, node, r, best.t, stack, sp, n_nodes);
-        if (at_leaf && (__popc(lm) >= leaf_min || nm == 0u)) leaf_step<COUNT>(sc.tri, node, r, best, stack, sp, n_tris);
+        // a lane that arrives at a leaf parks it and keeps walking: the triangle test is issued when enough lanes hold one
+        for (int k = 0; k < node_steps; k++) {
+            if (node >= 0) node_step<COUNT>(sc.qnodes, node, r, best.t, stack, sp, n_nodes);
+            if (node < 0 && node != MCPT_SENT && pend == 0) { pend = node; node = stack[--sp]; }
+        }
+        const bool has_p = pend != 0;
+        const bool blocked = has_p && node < 0;   // a second leaf, or nothing left but the parked one
+        const unsigned pm = __ballot_sync(0xffffffffu, has_p), bm = __ballot_sync(0xffffffffu, blocked);
+        const unsigned nm = __ballot_sync(0xffffffffu, node >= 0);
+        if (has_p && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) {
+            tri_test<COUNT>(sc.tri, ~pend, r, best, n_tris);
+            pend = 0;
+        }
     }
     if (has_ray) write_back();
     if (COUNT) {
@@ -310,60 +321,118 @@ int wavefront_slots(const RenderParams& P) {
 size_t wavefront_scratch_bytes(int n_slots, int n_lights) {
     const size_t n = (size_t)n_slots;
     return 6 * align256(16 * n) + align256(16 * n * (size_t)(n_lights > 0 ? n_lights : 1)) + align256(4 * n) +
-           2 * align256(16 * n * (size_t)(n_lights + 1)) + align256(4 * WFC_COUNT);
+           2 * align256(16 * n * (size_t)(n_lights + 1)) + align256(4 * WFC_COUNT * WF_MAX_PIPES);
 }
 
-// Runs the shade/trace loop until every slot is done.  h_alive: pinned host word for the termination check.
-int launch_wavefront(const RenderParams& P, int flags, void* scratch, unsigned* h_alive, cudaStream_t stream, int* launches,
-                     std::vector<cudaEvent_t>* trace_events, int* iterations) {
+void WfHost::destroy() {
+    for (cudaStream_t s : side_streams) cudaStreamDestroy(s);
+    for (cudaEvent_t e : events) cudaEventDestroy(e);
+    for (cudaEvent_t e : trace_events) cudaEventDestroy(e);
+    if (h_alive) cudaFreeHost(h_alive);
+    side_streams.clear(); events.clear(); trace_events.clear(); h_alive = nullptr;
+}
+
+// Runs the shade/trace loop until every slot is done.
+//
+// The slots are cut into `pipes` contiguous ranges, each with its own ray queue and counters, iterating independently
+// on its own stream: while one pipe's wf_trace drains its last long rays (ray lengths are heavy-tailed, so the tail of
+// a launch runs at low occupancy) the other pipes' kernels fill the SMs.  The host enqueues `batch` iterations per
+// pipe, then reads each pipe's live-slot count of the PREVIOUS batch, so the GPU never waits for the host.
+int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H, cudaStream_t stream, int* launches) {
     const int n_slots = wavefront_slots(P);
     const int nl = P.scene.n_lights;
     if (n_slots <= 0 || nl > WF_MAX_LIGHTS) return (int)cudaErrorInvalidConfiguration;
-    WfBuffers B{};
+    cudaError_t e;
+#define WF_CU(call) do { e = (call); if (e != cudaSuccess) return (int)e; } while (0)
+    int pipes = env_int("MCPT_WF_PIPES", 3);
+    pipes = pipes < 1 ? 1 : pipes > WF_MAX_PIPES ? WF_MAX_PIPES : pipes;
+    if (n_slots < 256 * 64 * pipes) pipes = 1;   // small images: one pipe already underfills the GPU
+    while ((int)H.side_streams.size() < pipes - 1) { cudaStream_t s; WF_CU(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)); H.side_streams.push_back(s); }
+    while ((int)H.events.size() < 2 + 3 * WF_MAX_PIPES) { cudaEvent_t ev; WF_CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); H.events.push_back(ev); }
+    if (!H.h_alive) WF_CU(cudaHostAlloc((void**)&H.h_alive, sizeof(unsigned) * 2 * WF_MAX_PIPES, cudaHostAllocDefault));
+
+    WfBuffers B0{};
     char* p = (char*)scratch;
     auto take = [&](size_t bytes) { char* r = p; p += align256(bytes); return r; };
     const size_t n = (size_t)n_slots;
-    B.hit = (float4*)take(16 * n); B.hit0 = (float4*)take(16 * n); B.sum_s = (float4*)take(16 * n);
-    B.beta_m = (float4*)take(16 * n); B.L = (float4*)take(16 * n); B.rd = (float4*)take(16 * n);
-    B.pend = (float4*)take(16 * n * (size_t)(nl > 0 ? nl : 1));
-    B.vis = (unsigned*)take(4 * n);
-    B.ray_o = (float4*)take(16 * n * (size_t)(nl + 1)); B.ray_d = (float4*)take(16 * n * (size_t)(nl + 1));
-    B.counters = (unsigned*)take(4 * WFC_COUNT);
-    B.n_slots = n_slots;
-    cudaError_t e = cudaMemsetAsync(B.counters, 0, 4 * WFC_COUNT, stream);
-    if (e != cudaSuccess) return (int)e;
-    const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
-    const int shade_blocks = (n_slots + 255) / 256;
-    const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 16);   // CTAs of 4 warps
-    const int refill_min = env_int("MCPT_REFILL_MIN", 8), leaf_min = env_int("MCPT_LEAF_MIN", 1);
-    int nlaunch = 0;
-    const int batch = 8;
-    for (int iter = 0;; iter++) {
-        if (reuse) wf_shade<true><<<shade_blocks, 256, 0, stream>>>(P, B, iter);
-        else wf_shade<false><<<shade_blocks, 256, 0, stream>>>(P, B, iter);
-        if (trace_events) {   // one event pair per wf_trace launch; the pool grows and is reused across renders
-            while (trace_events->size() < 2 * (size_t)(iter + 1)) {
-                cudaEvent_t ev; e = cudaEventCreate(&ev);
-                if (e != cudaSuccess) return (int)e;
-                trace_events->push_back(ev);
-            }
-            cudaEventRecord((*trace_events)[2 * iter], stream);
-        }
-        if (count) wf_trace<true><<<trace_blocks, 128, 0, stream>>>(P.scene, B, iter, P.counters, refill_min, leaf_min);
-        else wf_trace<false><<<trace_blocks, 128, 0, stream>>>(P.scene, B, iter, P.counters, refill_min, leaf_min);
-        if (trace_events) cudaEventRecord((*trace_events)[2 * iter + 1], stream);
-        nlaunch += 2;
-        if (iterations) *iterations = iter + 1;
-        if (iter % batch == batch - 1) {
-            e = cudaMemcpyAsync(h_alive, B.counters + WFC_ALIVE + (iter & 1), 4, cudaMemcpyDeviceToHost, stream);
-            if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-            if (e != cudaSuccess) return (int)e;
-            if (*h_alive == 0u) break;
-        }
-        if (iter > (1 << 24)) return (int)cudaErrorUnknown;
+    B0.hit = (float4*)take(16 * n); B0.hit0 = (float4*)take(16 * n); B0.sum_s = (float4*)take(16 * n);
+    B0.beta_m = (float4*)take(16 * n); B0.L = (float4*)take(16 * n); B0.rd = (float4*)take(16 * n);
+    B0.pend = (float4*)take(16 * n * (size_t)(nl > 0 ? nl : 1));
+    B0.vis = (unsigned*)take(4 * n);
+    B0.ray_o = (float4*)take(16 * n * (size_t)(nl + 1)); B0.ray_d = (float4*)take(16 * n * (size_t)(nl + 1));
+    B0.counters = (unsigned*)take(4 * WFC_COUNT * WF_MAX_PIPES);
+    B0.n_slots = n_slots;
+    WF_CU(cudaMemsetAsync(B0.counters, 0, 4 * WFC_COUNT * WF_MAX_PIPES, stream));
+
+    struct Pipe { WfBuffers B; cudaStream_t st; int shade_blocks; bool done; };
+    std::vector<Pipe> pp(pipes);
+    const int per = ((n_slots + pipes - 1) / pipes + 255) / 256 * 256;
+    for (int k = 0; k < pipes; k++) {
+        Pipe& q = pp[k];
+        q.B = B0;
+        q.B.slot_begin = k * per < n_slots ? k * per : n_slots;
+        q.B.slot_end = (k + 1) * per < n_slots ? (k + 1) * per : n_slots;
+        q.B.ray_o = B0.ray_o + (size_t)q.B.slot_begin * (nl + 1);
+        q.B.ray_d = B0.ray_d + (size_t)q.B.slot_begin * (nl + 1);
+        q.B.counters = B0.counters + WFC_COUNT * k;
+        q.st = k == 0 ? stream : H.side_streams[k - 1];
+        q.shade_blocks = (q.B.slot_end - q.B.slot_begin + 255) / 256;
+        q.done = q.shade_blocks == 0;
     }
+    // fork: the side streams start after everything already enqueued on `stream` (raygen, counter reset)
+    cudaEvent_t ev_fork = H.events[0];
+    WF_CU(cudaEventRecord(ev_fork, stream));
+    for (int k = 1; k < pipes; k++) WF_CU(cudaStreamWaitEvent(pp[k].st, ev_fork, 0));
+
+    const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
+    const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 16) / pipes;   // CTAs of 4 warps, shared by the pipes
+    const int refill_min = env_int("MCPT_REFILL_MIN", 16), leaf_min = env_int("MCPT_LEAF_MIN", 12),
+              block_min = env_int("MCPT_BLOCK_MIN", 4), node_steps = env_int("MCPT_NODE_STEPS", 4);
+    const int batch = 8;
+    int nlaunch = 0, n_timed = 0;
+    for (int b = 0;; b++) {
+        bool any = false;
+        for (int k = 0; k < pipes; k++) {
+            Pipe& q = pp[k];
+            if (q.done) continue;
+            any = true;
+            for (int iter = b * batch; iter < (b + 1) * batch; iter++) {
+                if (reuse) wf_shade<true><<<q.shade_blocks, 256, 0, q.st>>>(P, q.B, iter);
+                else wf_shade<false><<<q.shade_blocks, 256, 0, q.st>>>(P, q.B, iter);
+                while (H.trace_events.size() < 2 * (size_t)(n_timed + 1)) {   // one event pair per wf_trace launch, reused across renders
+                    cudaEvent_t ev; WF_CU(cudaEventCreate(&ev));
+                    H.trace_events.push_back(ev);
+                }
+                cudaEventRecord(H.trace_events[2 * n_timed], q.st);
+                if (count) wf_trace<true><<<trace_blocks, 128, 0, q.st>>>(P.scene, q.B, iter, P.counters, refill_min, leaf_min, block_min, node_steps);
+                else wf_trace<false><<<trace_blocks, 128, 0, q.st>>>(P.scene, q.B, iter, P.counters, refill_min, leaf_min, block_min, node_steps);
+                cudaEventRecord(H.trace_events[2 * n_timed + 1], q.st);
+                n_timed++; nlaunch += 2;
+            }
+            const int last = (b + 1) * batch - 1;
+            WF_CU(cudaMemcpyAsync(H.h_alive + 2 * k + (b & 1), q.B.counters + WFC_ALIVE + (last & 1), 4, cudaMemcpyDeviceToHost, q.st));
+            WF_CU(cudaEventRecord(H.events[2 + 2 * k + (b & 1)], q.st));
+        }
+        if (!any) break;
+        if (b > 0) {   // look at the batch before the one just enqueued
+            for (int k = 0; k < pipes; k++) {
+                if (pp[k].done) continue;
+                WF_CU(cudaEventSynchronize(H.events[2 + 2 * k + ((b - 1) & 1)]));
+                if (H.h_alive[2 * k + ((b - 1) & 1)] == 0u) pp[k].done = true;
+            }
+        }
+        if (b > (1 << 22)) return (int)cudaErrorUnknown;
+    }
+    // join: `stream` continues after every pipe has finished
+    for (int k = 1; k < pipes; k++) {
+        cudaEvent_t ev = H.events[2 + 2 * WF_MAX_PIPES + k];
+        WF_CU(cudaEventRecord(ev, pp[k].st));
+        WF_CU(cudaStreamWaitEvent(stream, ev, 0));
+    }
+    H.iterations = n_timed;
     if (launches) *launches += nlaunch;
     return (int)cudaGetLastError();
+#undef WF_CU
 }
 
 }  // namespace mcpt
