@@ -25,7 +25,10 @@ WORKLOADS = {
     "cornell-box-1024x1024-spp256": ("cornell-box", 0, 0, 256),
     "veach-mis-1200x900-spp100": ("veach-mis", 0, 0, 100),
     "cornell-box-3840x2160-spp1024": ("cornell-box", 3840, 2160, 1024),
+    "synthetic-5M-1920x1080-spp64": ("synthetic-5M", 1920, 1080, 64),
+    "synthetic-1M-1920x1080-spp64": ("synthetic-1M", 1920, 1080, 64),
 }
+SYNTHETIC_TRIS = {"synthetic-5M": 5_000_000, "synthetic-1M": 1_000_000}
 DEFAULT_WORKLOAD = "cornell-box-1024x1024-spp256"
 # bounded CPU sample of the same workload: same scene and camera, fewer pixels/samples (no pixel jitter in the
 # reference, so a lower resolution is a point-subsampling of the same image with the same cost per sample)
@@ -78,9 +81,25 @@ def cpu_reference_sample(scene_name, steps=1, warmup=0):
     oracle port when the reference binary did not travel.  Returns the cpu_baseline dict (value in Msamples/s)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle_py as O
+    times = []
+    if scene_name.startswith("synthetic"):
+        # the reference would need the mesh as a ~500 MB .obj; the CPU restatement (same algorithm, same balanced tree,
+        # Philox instead of the racy RNG) takes the in-memory scene instead: kind "port"
+        from montecarlopathtracing_b200.synthetic import make_scene
+        w, h, spp = 160, 90, 4
+        sample = "%s %dx%d spp %d (same camera, point-subsampled pixels)" % (scene_name, w, h, spp)
+        desc, keep, cam = make_scene(SYNTHETIC_TRIS[scene_name])
+        osc = O.OracleScene(desc)
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            osc.render(cam, spp, w, h)
+            if i >= warmup:
+                times.append((time.perf_counter() - t0) * 1e3)
+        ms = sum(times) / len(times)
+        return {"value": w * h * spp / ms * 1e-3, "unit": "Msamples/s", "cores": os.cpu_count(), "kind": "port", "sample": sample,
+                "ms_per_step": ms, "host_cpus": os.cpu_count()}
     w, h, spp = CPU_SAMPLE[scene_name]
     sample = "%s %dx%d spp %d (same camera, point-subsampled pixels)" % (scene_name, w, h, spp)
-    times = []
     if O.have_ref():
         for i in range(warmup + steps):
             _, ms = O.ref_image(O.REF_SCENE_DIR + scene_name, spp, w, h)
@@ -136,18 +155,24 @@ def run_ours(args):
 
     scene_name, width, height, spp_per_gpu = WORKLOADS[args.workload]
     spp = spp_per_gpu * world
-    s = M.HostScene(os.path.join(ROOT, "scenes") + "/", scene_name)
-    w = width or s.camera.width
-    h = height or s.camera.height
+    if scene_name.startswith("synthetic"):
+        from montecarlopathtracing_b200.synthetic import make_scene
+        src_desc, keep, camera = make_scene(SYNTHETIC_TRIS[scene_name], width=width, height=height)
+        arrays, textures, n_faces, n_lights = keep[:4], [], src_desc.n_faces, src_desc.n_lights
+    else:
+        s = M.HostScene(os.path.join(ROOT, "scenes") + "/", scene_name)
+        src_desc, camera, arrays, textures, n_faces, n_lights = s.desc, s.camera, (s.pos, s.nrm, s.uv, s.mat_id), s.textures, s.n_faces, len(s.lights)
+    w = width or camera.width
+    h = height or camera.height
     # host inputs in pinned memory (the e2e leg copies them to the device every step)
-    pinned = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in (s.pos, s.nrm, s.uv, s.mat_id)]
+    pinned = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in arrays]
     desc = _capi.SceneDesc()
-    ctypes.memmove(ctypes.byref(desc), ctypes.byref(s.desc), ctypes.sizeof(desc))
+    ctypes.memmove(ctypes.byref(desc), ctypes.byref(src_desc), ctypes.sizeof(desc))
     desc.pos = ctypes.cast(pinned[0].data_ptr(), ctypes.POINTER(ctypes.c_double))
     desc.nrm = ctypes.cast(pinned[1].data_ptr(), ctypes.POINTER(ctypes.c_double))
     desc.uv = ctypes.cast(pinned[2].data_ptr(), ctypes.POINTER(ctypes.c_double))
     desc.mat_id = ctypes.cast(pinned[3].data_ptr(), ctypes.POINTER(ctypes.c_int32))
-    tex_bytes = sum(t.height * t.width * 3 for t in s.textures)
+    tex_bytes = sum(t.height * t.width * 3 for t in textures)
     h2d = sum(p.numel() * p.element_size() for p in pinned) + tex_bytes
     host_img = torch.empty(h * w * 3, dtype=torch.float32).pin_memory()
 
@@ -157,7 +182,7 @@ def run_ours(args):
     ctx.set_seed(2026)
     ctx.upload_scene(desc)
     mode = M.MODE_WAVEFRONT if args.mode == "wavefront" else M.MODE_MEGAKERNEL
-    render_partial, sum_partials, stats = gpu_backend(ctx, s.camera, spp, w, h, mode=mode)
+    render_partial, sum_partials, stats = gpu_backend(ctx, camera, spp, w, h, mode=mode)
 
     def barrier():
         if world > 1:
@@ -221,7 +246,7 @@ def run_ours(args):
         # algorithmic bytes of the dominant kernel: 32 B per node fetch + 48 B per triangle test, counted
         # by the COUNT variant on the same workload at reduced spp (per-ray averages are spp-independent)
         cspp = max(8, min(spp_per_gpu, 16))
-        ctx.render(s.camera, cspp, w, h, mode=mode, flags=M.FLAG_COUNT)
+        ctx.render(camera, cspp, w, h, mode=mode, flags=M.FLAG_COUNT)
         cs = ctx.last_stats
         bytes_per_ray = (32.0 * cs.node_visits + 48.0 * cs.tri_tests) / cs.rays
         # dominant kernel: the megakernel (one launch per step), or wf_trace (one launch per wavefront iteration; its
@@ -238,12 +263,13 @@ def run_ours(args):
         line = {
             "metric": "path-tracing throughput", "value": samples / ms_total * 1e-3, "unit": "Msamples/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "shipped scene (scenes/%s.obj)" % scene_name,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": ("synthetic mesh (montecarlopathtracing_b200/synthetic.py, seed 1234)" if scene_name.startswith("synthetic")
+                                                               else "shipped scene (scenes/%s.obj)" % scene_name),
             "config": {"workload": args.workload, "scene": scene_name, "width": w, "height": h, "spp_total": spp,
                        "spp_per_gpu": spp_per_gpu, "mode": args.mode, "partition": "spp-split, 8 chunks, fixed-tree sum",
                        "l2_policy": "no flush: the scene (%.1f MB of nodes+triangles) is L1/L2-resident by design and every "
                                     "launch re-reads it millions of times; the wavefront state and ray queues (~%d MB) "
-                                    "exceed L2 at this size" % ((32 + 48 + 64) * s.n_faces / 1e6, int(w * h * (100 + 16 * len(s.lights) + 32 * (len(s.lights) + 1)) / 1e6))},
+                                    "exceed L2 at this size" % ((32 + 48 + 64) * n_faces / 1e6, int(w * h * (100 + 16 * n_lights + 32 * (n_lights + 1)) / 1e6))},
             "mrays_per_s": rays_total / ms_total * 1e-3, "rays_per_sample": rays_total / samples,
             "lbvh_build_ms": sum(build_ms) / len(build_ms), "render_ms": sum(render_ms) / len(render_ms),
             "e2e": {"value": samples / e2e_ms * 1e-3, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
