@@ -272,6 +272,10 @@ def run_ours(args):
                                     "exceed L2 at this size" % ((32 + 48 + 64) * n_faces / 1e6, int(w * h * (100 + 16 * n_lights + 32 * (n_lights + 1)) / 1e6))},
             "mrays_per_s": rays_total / ms_total * 1e-3, "rays_per_sample": rays_total / samples,
             "lbvh_build_ms": sum(build_ms) / len(build_ms), "render_ms": sum(render_ms) / len(render_ms),
+            # seam 1: 528 algorithmic bytes per triangle over the nine build launches against the HBM peak
+            "lbvh_build_roofline": {"bound": "hbm", "achieved": 528.0 * n_faces / (sum(build_ms) / len(build_ms) * 1e-3) / 1e9,
+                                    "peak": pk["hbm_gbs"], "unit": "GB/s",
+                                    "frac": 528.0 * n_faces / (sum(build_ms) / len(build_ms) * 1e-3) / 1e9 / pk["hbm_gbs"]},
             "e2e": {"value": samples / e2e_ms * 1e-3, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": h * w * 3 * 4, "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": launches,
