@@ -157,6 +157,9 @@ MCPT_API int mcpt_get_morton(mcpt_ctx* ctx, uint32_t* codes_obj_order, uint32_t*
 /* The built tree, for structural tests: n_faces-1 internal nodes x 16 floats
  * (see DESIGN.md "node layout"); parent[n_faces-1]; root index. */
 MCPT_API int mcpt_get_nodes(mcpt_ctx* ctx, float* nodes16, int32_t* root);
+/* The tree traversal walks: the radix tree's leaves re-clustered by surface area (PLOC), same node format
+ * and leaf indices; root is n_faces-2.  With MCPT_BVH=lbvh in the environment it is the radix tree itself. */
+MCPT_API int mcpt_get_traversal_tree(mcpt_ctx* ctx, float* nodes16, int32_t* root);
 
 /* Seam 2. Closest hit of n rays, HOST buffers: org_dir = n x 6 floats (origin, direction; the
  * direction need not be unit).  Tie rule and the d.x==0 quirk follow MTPC/pathTracing.cpp:347-361. */

@@ -132,6 +132,13 @@ class Context:
         check(lib().mcpt_get_nodes(self._c, nodes.ctypes.data, C.byref(root)))
         return nodes, root.value
 
+    def get_traversal_tree(self):
+        nn = max(self.n_faces - 1, 1)
+        nodes = np.empty((nn, 16), np.float32)
+        root = C.c_int32()
+        check(lib().mcpt_get_traversal_tree(self._c, nodes.ctypes.data, C.byref(root)))
+        return nodes, root.value
+
     def trace(self, org_dir):
         """org_dir: (n,6) float32 host array -> structured array of hits (t,u,v,tri,leaf)."""
         rays = np.ascontiguousarray(org_dir, dtype=np.float32).reshape(-1, 6)

@@ -2,6 +2,7 @@
 // No CPU fallback: every entry point that computes needs a CUDA device with sm_100a code.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -58,7 +59,8 @@ void free_scene(mcpt_ctx* c) {
     SceneBuffers& s = c->sb;
     cudaFree(s.pos); cudaFree(s.nrm); cudaFree(s.uv); cudaFree(s.mat_id); cudaFree(s.codes_obj); cudaFree(s.codes_sorted);
     cudaFree(s.iota); cudaFree(s.leaf_face); cudaFree(s.leaf_parent); cudaFree(s.flags); cudaFree(s.nodes); cudaFree(s.tri);
-    cudaFree(s.shade); cudaFree(s.root_box); cudaFree(s.cub_temp); cudaFree(s.qnodes); cudaFree(s.qgrid);
+    cudaFree(s.shade); cudaFree(s.root_box); cudaFree(s.cub_temp); cudaFree(s.qnodes); cudaFree(s.qgrid); cudaFree(s.nodes2); cudaFree(s.cl_lo[0]); cudaFree(s.cl_lo[1]); cudaFree(s.cl_hi[0]);
+    cudaFree(s.cl_hi[1]); cudaFree(s.ploc_nn); cudaFree(s.ploc_flag); cudaFree(s.ploc_scan); cudaFree(s.ploc_temp); cudaFree(s.ploc_state);
     s = SceneBuffers();
     cudaFree(c->d_materials); cudaFree(c->d_textures); cudaFree(c->d_tex_bytes); cudaFree(c->d_lights);
     cudaFree(c->d_light_tris); cudaFree(c->d_light_cdf);
@@ -77,7 +79,7 @@ double face_area(const double* p) {
 DeviceScene device_scene(const mcpt_ctx* c) {
     DeviceScene d{};
     d.n_faces = c->sb.n_faces; d.n_materials = c->n_materials; d.n_textures = c->n_textures; d.n_lights = c->n_lights;
-    d.root = 0; d.area0 = c->area0;
+    d.root = c->sb.root; d.area0 = c->area0;
     d.nodes = c->sb.nodes; d.qnodes = c->sb.qnodes; d.qgrid = c->sb.qgrid; d.tri = c->sb.tri; d.shade = c->sb.shade; d.leaf_face = c->sb.leaf_face; d.pos = c->sb.pos;
     d.materials = c->d_materials; d.textures = c->d_textures; d.tex_bytes = c->d_tex_bytes;
     d.lights = c->d_lights; d.light_tris = c->d_light_tris; d.light_cdf = c->d_light_cdf;
@@ -152,6 +154,12 @@ MCPT_API int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     CU(dev_alloc(s.codes_obj, N)); CU(dev_alloc(s.codes_sorted, N)); CU(dev_alloc(s.iota, N)); CU(dev_alloc(s.leaf_face, N));
     CU(dev_alloc(s.leaf_parent, N)); CU(dev_alloc(s.flags, N)); CU(dev_alloc(s.nodes, N)); CU(dev_alloc(s.tri, N));
     CU(dev_alloc(s.shade, N)); CU(dev_alloc(s.root_box, 6)); CU(dev_alloc(s.qnodes, N)); CU(dev_alloc(s.qgrid, 1));
+    CU(dev_alloc(s.nodes2, N)); CU(dev_alloc(s.cl_lo[0], N)); CU(dev_alloc(s.cl_lo[1], N)); CU(dev_alloc(s.cl_hi[0], N)); CU(dev_alloc(s.cl_hi[1], N));
+    CU(dev_alloc(s.ploc_nn, N)); CU(dev_alloc(s.ploc_flag, N)); CU(dev_alloc(s.ploc_scan, N));
+    s.ploc_temp_bytes = ploc_scan_temp_bytes(n);
+    CU(cudaMalloc(&s.ploc_temp, s.ploc_temp_bytes ? s.ploc_temp_bytes : 1));
+    CU(cudaMalloc(&s.ploc_state, 64));
+    { const char* v = getenv("MCPT_BVH"); s.use_ploc = !(v && std::strcmp(v, "lbvh") == 0); }
     s.cub_temp_bytes = lbvh_sort_temp_bytes(n);
     CU(cudaMalloc(&s.cub_temp, s.cub_temp_bytes ? s.cub_temp_bytes : 1));
     cudaStream_t st = c->stream;
@@ -259,6 +267,17 @@ MCPT_API int mcpt_get_nodes(mcpt_ctx* c, float* nodes16, int32_t* root) {
     const int n_nodes = c->sb.n_faces > 1 ? c->sb.n_faces - 1 : 1;
     if (nodes16) CU(cudaMemcpy(nodes16, c->sb.nodes, sizeof(BvhNode) * (size_t)n_nodes, cudaMemcpyDeviceToHost));
     if (root) *root = 0;
+    return MCPT_OK;
+}
+
+MCPT_API int mcpt_get_traversal_tree(mcpt_ctx* c, float* nodes16, int32_t* root) {
+    if (!c || !c->sb.built) return fail_arg("mcpt_get_traversal_tree: build the BVH first");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    const int n_nodes = c->sb.n_faces > 1 ? c->sb.n_faces - 1 : 1;
+    const BvhNode* src = (c->sb.use_ploc && c->sb.n_faces >= 2) ? c->sb.nodes2 : c->sb.nodes;
+    if (nodes16) CU(cudaMemcpy(nodes16, src, sizeof(BvhNode) * (size_t)n_nodes, cudaMemcpyDeviceToHost));
+    if (root) *root = c->sb.root;
     return MCPT_OK;
 }
 

@@ -102,7 +102,8 @@ __global__ void __launch_bounds__(256) emit_refit_kernel(int n, const double* __
                                                          const double* __restrict__ uv, const int* __restrict__ mat_id,
                                                          const int* __restrict__ leaf_face, const int* __restrict__ leaf_parent,
                                                          BvhNode* nodes, unsigned* flags, TriGeom* __restrict__ tri,
-                                                         TriShade* __restrict__ shade, float* __restrict__ root_box) {
+                                                         TriShade* __restrict__ shade, float* __restrict__ root_box,
+                                                         float4* __restrict__ cl_lo, float4* __restrict__ cl_hi) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     const int f = leaf_face[k];
@@ -131,6 +132,8 @@ __global__ void __launch_bounds__(256) emit_refit_kernel(int n, const double* __
         const float pad = 4.0e-7f * fmaxf(fabsf(lo), fabsf(hi)) + 1.0e-30f;  // > 3 ulp: covers v0+e1 rounding and slab rounding
         b.lo[a] = lo - pad; b.hi[a] = hi + pad;
     }
+    cl_lo[k] = make_float4(b.lo[0], b.lo[1], b.lo[2], __int_as_float(~k));   // leaf cluster of the quality pass (ploc.cu)
+    cl_hi[k] = make_float4(b.hi[0], b.hi[1], b.hi[2], 0.0f);
     if (n == 1) {  // degenerate tree: node 0 points at the only leaf twice
         store_child_box(&nodes[0], 0, b); store_child_box(&nodes[0], 1, b);
         int* c = reinterpret_cast<int*>(&nodes[0].q[3]);
@@ -221,9 +224,16 @@ int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches) {
         radix_tree_kernel<<<(n - 1 + tpb - 1) / tpb, tpb, 0, stream>>>(sb.codes_sorted, n, sb.nodes, sb.leaf_parent); nl++;
     }
     emit_refit_kernel<<<(n + tpb - 1) / tpb, tpb, 0, stream>>>(n, sb.pos, sb.nrm, sb.uv, sb.mat_id, sb.leaf_face, sb.leaf_parent,
-                                                               sb.nodes, sb.flags, sb.tri, sb.shade, sb.root_box); nl++;
+                                                               sb.nodes, sb.flags, sb.tri, sb.shade, sb.root_box, sb.cl_lo[0], sb.cl_hi[0]); nl++;
     const int n_nodes = n > 1 ? n - 1 : 1;
-    quantize_nodes_kernel<<<(n_nodes + tpb - 1) / tpb, tpb, 0, stream>>>(n_nodes, sb.nodes, sb.root_box, sb.qnodes, sb.qgrid); nl++;
+    const BvhNode* walk = sb.nodes;
+    sb.root = 0;
+    if (sb.use_ploc && n >= 2) {
+        const int pe = ploc_build(sb, stream, &nl);
+        if (pe) return pe;
+        walk = sb.nodes2; sb.root = n - 2;
+    }
+    quantize_nodes_kernel<<<(n_nodes + tpb - 1) / tpb, tpb, 0, stream>>>(n_nodes, walk, sb.root_box, sb.qnodes, sb.qgrid); nl++;
     if (launches) *launches = nl;
     sb.built = true;
     return (int)cudaGetLastError();

@@ -22,6 +22,13 @@ struct SceneBuffers {
     QNode* qnodes = nullptr;           // traversal nodes, same indexing as `nodes`
     QGrid* qgrid = nullptr;
     void* cub_temp = nullptr; size_t cub_temp_bytes = 0;
+    // quality pass (ploc.cu): the tree traversal walks
+    bool use_ploc = true;              // MCPT_BVH=lbvh keeps the radix tree for traversal (A/B measurements)
+    BvhNode* nodes2 = nullptr;         // PLOC tree, n-1 nodes, root = n-2
+    float4* cl_lo[2] = {nullptr, nullptr}; float4* cl_hi[2] = {nullptr, nullptr};   // cluster boxes (+ref in lo.w), ping-pong
+    int* ploc_nn = nullptr; unsigned long long* ploc_flag = nullptr; unsigned long long* ploc_scan = nullptr;
+    void* ploc_temp = nullptr; size_t ploc_temp_bytes = 0; void* ploc_state = nullptr;
+    int root = 0;                      // root of the traversal tree (0: radix tree, n-2: PLOC tree)
     bool built = false;
 };
 
@@ -30,5 +37,8 @@ size_t lbvh_sort_temp_bytes(int n);
 // K1 Morton -> CUB radix sort -> K2 radix tree -> K3 leaf emit + atomic bottom-up refit -> K4 node quantisation.
 // Returns a cudaError_t as int; all work is enqueued on `stream`.
 int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches);
+// K4a (ploc.cu): parallel locally-ordered clustering over the Morton-ordered leaf boxes -> sb.nodes2.
+size_t ploc_scan_temp_bytes(int n);
+int ploc_build(SceneBuffers& sb, cudaStream_t stream, int* launches);
 
 }  // namespace mcpt

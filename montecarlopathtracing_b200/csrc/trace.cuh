@@ -24,12 +24,14 @@ struct Hit { float t, u, v; int k; };  // k = sorted-leaf index, -1 = miss
 // cracks; which of two edge-sharing triangles wins is then decided by t like in the reference.
 #define MCPT_EDGE_EPS 2.0e-6f
 
+__device__ __forceinline__ bool a_pos(float a) { return !(a < 0.0f); }
+
 // Per-ray constants.  Slab planes come from the 16-bit grid of the quantised nodes: a plane with grid coordinate q is
 // crossed at t = (origin + q*cell - o) / d = q*a + b with a = cell/d, b = (origin - o)/d.  q is turned into a float by
 // the magic-number trick — PRMT drops its 16 bits into the mantissa of 2^23, giving the float 2^23 + q exactly — so
 // t = (2^23 + q)*a + (b - 2^23*a): one PRMT and one FMA per plane.  b' = b - 2^23*a is rounded to half a grid cell
 // at worst, which the two-cell outward push of the quantiser covers (lbvh.cu K4).
-struct RayCtx { float3 o, d; float ax, ay, az, bx, by, bz; };
+struct RayCtx { float3 o, d; float ax, ay, az, bx, by, bz; unsigned sx, sy, sz; };
 
 __device__ __forceinline__ RayCtx ray_setup(const float3 o, const float3 d, const QGrid* __restrict__ grid) {
     RayCtx r; r.o = o; r.d = d;
@@ -42,6 +44,9 @@ __device__ __forceinline__ RayCtx ray_setup(const float3 o, const float3 d, cons
     r.bx = fmaf(-8388608.0f, r.ax, (go.x - o.x) * idx);
     r.by = fmaf(-8388608.0f, r.ay, (go.y - o.y) * idy);
     r.bz = fmaf(-8388608.0f, r.az, (go.z - o.z) * idz);
+    // PRMT selectors of the NEAR plane per axis: the low half (lo) when the ray travels in +axis, else the high half
+    // (hi); the far plane's selector is the near one ^ 0x0022.  Saves the six min/max per child that order lo and hi.
+    r.sx = a_pos(r.ax) ? 0x7410u : 0x7432u; r.sy = a_pos(r.ay) ? 0x7410u : 0x7432u; r.sz = a_pos(r.az) ? 0x7410u : 0x7432u;
     return r;
 }
 
@@ -50,6 +55,7 @@ __device__ __forceinline__ RayCtx ray_setup(const float3 o, const float3 d, cons
 
 __device__ __forceinline__ float q_lo(unsigned w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7410)); }
 __device__ __forceinline__ float q_hi(unsigned w) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7432)); }
+__device__ __forceinline__ float q_sel(unsigned w, unsigned sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)); }
 
 // One internal-node step: fetch the 32-B node (two 16-B loads, one sector), slab-test both children against
 // [0, best_t], descend into the nearer hit child (pushing the farther) or pop.  `node` >= 0 on entry.
@@ -59,16 +65,17 @@ __device__ __forceinline__ void node_step(const QNode* __restrict__ nodes, int& 
     const uint4 k0 = __ldg(&nodes[node].c[0]);
     const uint4 k1 = __ldg(&nodes[node].c[1]);
     if (COUNT) n_nodes++;
-    const float a0 = fmaf(q_lo(k0.x), r.ax, r.bx), b0 = fmaf(q_hi(k0.x), r.ax, r.bx);
-    const float a1 = fmaf(q_lo(k0.y), r.ay, r.by), b1 = fmaf(q_hi(k0.y), r.ay, r.by);
-    const float a2 = fmaf(q_lo(k0.z), r.az, r.bz), b2 = fmaf(q_hi(k0.z), r.az, r.bz);
-    const float c0min = fmaxf(fmaxf(fminf(a0, b0), fminf(a1, b1)), fmaxf(fminf(a2, b2), 0.0f));
-    const float c0max = fminf(fminf(fmaxf(a0, b0), fmaxf(a1, b1)), fminf(fmaxf(a2, b2), best_t));
-    const float e0 = fmaf(q_lo(k1.x), r.ax, r.bx), f0 = fmaf(q_hi(k1.x), r.ax, r.bx);
-    const float e1 = fmaf(q_lo(k1.y), r.ay, r.by), f1 = fmaf(q_hi(k1.y), r.ay, r.by);
-    const float e2 = fmaf(q_lo(k1.z), r.az, r.bz), f2 = fmaf(q_hi(k1.z), r.az, r.bz);
-    const float c1min = fmaxf(fmaxf(fminf(e0, f0), fminf(e1, f1)), fmaxf(fminf(e2, f2), 0.0f));
-    const float c1max = fminf(fminf(fmaxf(e0, f0), fmaxf(e1, f1)), fminf(fmaxf(e2, f2), best_t));
+    const unsigned fx = r.sx ^ 0x0022u, fy = r.sy ^ 0x0022u, fz = r.sz ^ 0x0022u;
+    const float n0x = fmaf(q_sel(k0.x, r.sx), r.ax, r.bx), f0x = fmaf(q_sel(k0.x, fx), r.ax, r.bx);
+    const float n0y = fmaf(q_sel(k0.y, r.sy), r.ay, r.by), f0y = fmaf(q_sel(k0.y, fy), r.ay, r.by);
+    const float n0z = fmaf(q_sel(k0.z, r.sz), r.az, r.bz), f0z = fmaf(q_sel(k0.z, fz), r.az, r.bz);
+    const float c0min = fmaxf(fmaxf(n0x, n0y), fmaxf(n0z, 0.0f));
+    const float c0max = fminf(fminf(f0x, f0y), fminf(f0z, best_t));
+    const float n1x = fmaf(q_sel(k1.x, r.sx), r.ax, r.bx), f1x = fmaf(q_sel(k1.x, fx), r.ax, r.bx);
+    const float n1y = fmaf(q_sel(k1.y, r.sy), r.ay, r.by), f1y = fmaf(q_sel(k1.y, fy), r.ay, r.by);
+    const float n1z = fmaf(q_sel(k1.z, r.sz), r.az, r.bz), f1z = fmaf(q_sel(k1.z, fz), r.az, r.bz);
+    const float c1min = fmaxf(fmaxf(n1x, n1y), fmaxf(n1z, 0.0f));
+    const float c1max = fminf(fminf(f1x, f1y), fminf(f1z, best_t));
     const bool h0 = c0min <= c0max, h1 = c1min <= c1max;
     const int c0 = (int)k0.w, c1 = (int)k1.w;
     if (h0 && h1) {

@@ -232,8 +232,11 @@ __global__ void __launch_bounds__(256) wf_shade(const RenderParams P, const WfBu
 // from the queue head with one atomic for the warp.  Every loop iteration is one traversal step per lane: lanes at
 // an internal node take a node step; lanes at a leaf take a leaf step once `leaf_min` lanes have gathered there (or
 // no lane is at a node), so the triangle test is not issued for one or two lanes at a time.
+#ifndef MCPT_TRACE_MIN_CTAS
+#define MCPT_TRACE_MIN_CTAS 8
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(128) wf_trace(const DeviceScene sc, const WfBuffers B, const int iter, unsigned long long* stats,
+__global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const DeviceScene sc, const WfBuffers B, const int iter, unsigned long long* stats,
                                                 const int refill_min, const int leaf_min, const int block_min,
                                                 const int node_steps) {
     const int par = iter & 1;

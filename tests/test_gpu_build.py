@@ -110,3 +110,68 @@ def test_large_mesh_sorted_and_idempotent(gpu_ctx, oracle):
     gpu_ctx.build_bvh()
     c2, s2, f2 = gpu_ctx.get_morton()
     assert np.array_equal(f1, f2) and np.array_equal(s1, s2)
+
+
+def check_traversal_tree(nodes, root, n, tri_lo, tri_hi):
+    """The tree traversal walks (PLOC over the Morton-ordered leaves): every leaf reachable exactly once from the root,
+    n-1 internal nodes all used, every child box contains its subtree's triangles and is tight."""
+    child = nodes[:, 12:14].view(np.int32)
+    seen_leaf, seen_node = np.zeros(n, np.int32), np.zeros(len(nodes), np.int32)
+    def box_of(i, slot):
+        q = nodes[i]
+        return np.array([q[4 * slot + 0], q[4 * slot + 2], q[8 + 2 * slot]]), np.array([q[4 * slot + 1], q[4 * slot + 3], q[9 + 2 * slot]])
+    result, depth_max = {}, 0
+    stack = [(root, False, 1)]
+    while stack:
+        i, done, depth = stack.pop()
+        depth_max = max(depth_max, depth)
+        if not done:
+            seen_node[i] += 1
+            stack.append((i, True, depth))
+            for c in child[i]:
+                if c >= 0:
+                    stack.append((int(c), False, depth + 1))
+            continue
+        lo_all, hi_all = np.full(3, np.inf), np.full(3, -np.inf)
+        for slot, c in enumerate(child[i]):
+            blo, bhi = box_of(i, slot)
+            if c < 0:
+                k = ~int(c); seen_leaf[k] += 1
+                lo, hi = tri_lo[k], tri_hi[k]
+            else:
+                lo, hi = result.pop(int(c))
+            assert np.all(blo <= lo) and np.all(bhi >= hi), "child box does not contain its subtree"
+            assert np.all(blo >= lo - 1e-5 * (1 + np.abs(lo))) and np.all(bhi <= hi + 1e-5 * (1 + np.abs(hi))), "box not tight"
+            lo_all = np.minimum(lo_all, lo); hi_all = np.maximum(hi_all, hi)
+        result[i] = (lo_all, hi_all)
+    assert np.all(seen_leaf == 1) and np.all(seen_node == 1)
+    assert depth_max < 64, "traversal stack is 64 entries deep"
+    return depth_max
+
+
+@pytest.mark.parametrize("name", SCENE_NAMES)
+def test_traversal_tree_invariants_on_shipped_scenes(gpu_ctx, scenes, name):
+    s = scenes[name]
+    gpu_ctx.upload_scene(s)
+    gpu_ctx.build_bvh()
+    _, _, face_sorted = gpu_ctx.get_morton()
+    nodes, root = gpu_ctx.get_traversal_tree()
+    assert root == s.n_faces - 2 and nodes.shape == (s.n_faces - 1, 16)
+    p = s.pos[face_sorted].astype(np.float32).astype(np.float64)
+    check_traversal_tree(nodes, root, s.n_faces, p.min(axis=1), p.max(axis=1))
+    # rebuilding gives the same tree bit for bit (node numbering comes from scans, not from atomics)
+    gpu_ctx.build_bvh()
+    nodes2, _ = gpu_ctx.get_traversal_tree()
+    assert np.array_equal(nodes.view(np.uint32), nodes2.view(np.uint32))
+
+
+@pytest.mark.parametrize("n", [2, 3, 7, 64, 1001, 1025, 5000])
+def test_traversal_tree_small_counts(gpu_ctx, n):
+    """Sizes around the single-CTA finish threshold (1024) and many equal boxes (far_outside: all codes equal)."""
+    desc, keep = random_soup(n, seed=n, far_outside=(n == 64))
+    gpu_ctx.upload_scene(desc)
+    gpu_ctx.build_bvh()
+    _, _, face_sorted = gpu_ctx.get_morton()
+    nodes, root = gpu_ctx.get_traversal_tree()
+    p = keep[0].reshape(n, 3, 3)[face_sorted].astype(np.float32).astype(np.float64)
+    check_traversal_tree(nodes, root, n, p.min(axis=1), p.max(axis=1))

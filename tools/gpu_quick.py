@@ -23,6 +23,9 @@ for name, spp in (("cornell-box", 64), ("veach-mis", 32)):
         print("%s mode %d spp %d: integrate %.2f ms (trace %.2f ms in %d launches), %.1f Msamples/s, %.1f Mrays/s" %
               (name, mode, spp, st.integrate_ms, st.trace_ms, st.trace_launches, st.samples / st.render_ms * 1e-3,
                st.rays / st.render_ms * 1e-3), flush=True)
+    ctx.render(s.camera, 8, mode=modes[-1], flags=M.FLAG_COUNT)
+    st = ctx.last_stats
+    print("  counts: %.2f nodes/ray %.2f tris/ray %.3f rays/sample" % (st.node_visits / st.rays, st.tri_tests / st.rays, st.rays / st.samples))
     if len(imgs) == 2:
         a, b = imgs.values()
         print("  modes bit-identical:", bool(np.array_equal(a, b)), "mean", a.mean(axis=(0, 1)))
