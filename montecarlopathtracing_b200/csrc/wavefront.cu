@@ -6,7 +6,7 @@
 //   wf_shade  one thread per path SLOT.  Consumes the slot's ray results, advances the path state machine of
 //             shade() (MTPC/pathTracing.cpp:137-266) to the next vertex and emits ALL rays of that vertex at once —
 //             one shadow ray per light (NEE) plus the extend ray; their Philox numbers do not depend on each other —
-//             into a ray queue compacted with warp ballot/popc (one atomic per warp and ray kind).
+//             into a ray queue compacted with warp ballot/popc and a per-CTA prefix (one atomic per CTA and ray kind).
 //   wf_trace  one thread per queued ray: closest hit; extend/primary rays write the hit back to their slot, shadow
 //             rays set the slot's visibility bit when the closest hit carries the light's material (:212-215).
 // A slot owns (pixel, group of sample chunks) for the whole render, like a megakernel thread: it walks its samples in
@@ -49,17 +49,26 @@ __device__ __forceinline__ unsigned pack_meta(int state, int lobe, bool ext, boo
     return (unsigned)state | ((unsigned)lobe << 2) | ((unsigned)ext << 4) | ((unsigned)have0 << 5) | (bounce << 8) | ((unsigned)chunk << 16);
 }
 
-// Append a ray for every lane with pred set: one atomic per warp, slots in lane order.  Must be called by all 32 lanes.
+// Append a ray for every thread of the CTA with pred set: warp ballots, a shared-memory prefix over the CTA's warps and ONE
+// atomic on the queue tail per CTA and call (ncu: with one atomic per warp, 37 % of wf_shade's stall samples sat on the
+// return of that same-address atomic).  Rays keep thread order inside the CTA's segment.  Must be called by ALL threads
+// of the CTA; `call` alternates the shared scratch so consecutive calls need no extra barrier.
+struct PushScratch { unsigned cnt[2][8]; unsigned base[2]; };
 __device__ __forceinline__ void push_ray(const bool pred, const WfBuffers& B, unsigned* tail, const float3 o, const float3 d,
-                                         const float tmax, const unsigned id) {
+                                         const float tmax, const unsigned id, PushScratch& sh, const int call) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, buf = call & 1;
     const unsigned mask = __ballot_sync(0xffffffffu, pred);
-    if (mask == 0u) return;
-    const int lane = threadIdx.x & 31;
-    unsigned base = 0;
-    if (lane == __ffs(mask) - 1) base = atomicAdd(tail, (unsigned)__popc(mask));
-    base = __shfl_sync(0xffffffffu, base, __ffs(mask) - 1);
+    if (lane == 0) sh.cnt[buf][warp] = (unsigned)__popc(mask);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned total = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++) { const unsigned c = sh.cnt[buf][w]; sh.cnt[buf][w] = total; total += c; }
+        sh.base[buf] = total ? atomicAdd(tail, total) : 0u;
+    }
+    __syncthreads();
     if (pred) {
-        const unsigned i = base + __popc(mask & ((1u << lane) - 1u));
+        const unsigned i = sh.base[buf] + sh.cnt[buf][warp] + __popc(mask & ((1u << lane) - 1u));
         __stcg(&B.ray_o[i], make_float4(o.x, o.y, o.z, tmax));
         __stcg(&B.ray_d[i], make_float4(d.x, d.y, d.z, __uint_as_float(id)));
     }
@@ -80,6 +89,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
     if (slot == B.slot_begin) {   // the other parity's counters were last used by iteration iter-1, which has completed
         B.counters[WFC_TAIL + (par ^ 1)] = 0u; B.counters[WFC_ALIVE + (par ^ 1)] = 0u; B.counters[WFC_HEAD + (par ^ 1)] = 0u;
     }
+    __shared__ PushScratch push_sh;
     const int lane = threadIdx.x & 31;
     const int warp_id = slot >> 5;
     const int group = warp_id / n_tiles, tile = warp_id % n_tiles;
@@ -195,7 +205,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
             ok = sample_light(sc, sc.lights[l], vx, u, o, d, tmax, contrib);
             if (ok) { const float3 bp = mul_rn(beta, contrib); __stcg(&B.pend[(size_t)l * B.n_slots + slot], make_float4(bp.x, bp.y, bp.z, 0.f)); }
         }
-        push_ray(ok, B, tail, o, d, tmax, (unsigned)slot | ((unsigned)(l + 1) << WF_ID_BITS));
+        push_ray(ok, B, tail, o, d, tmax, (unsigned)slot | ((unsigned)(l + 1) << WF_ID_BITS), push_sh, l);
     }
     {
         bool ext = false;
@@ -210,7 +220,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
             }
             has_extend = ext;
         }
-        push_ray(ext || emit_primary, B, tail, o, d, 3.0e38f, (unsigned)slot);
+        push_ray(ext || emit_primary, B, tail, o, d, 3.0e38f, (unsigned)slot, push_sh, nl);
     }
     // ---- store the slot ----
     if (valid) {
@@ -228,8 +238,8 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
     } else if (slot < B.slot_end && iter == 0) {
         __stcg(&B.beta_m[slot], make_float4(0.f, 0.f, 0.f, __uint_as_float(pack_meta(WF_DONE, 0, false, false, 0, 0))));
     }
-    const unsigned alive = __ballot_sync(0xffffffffu, valid && state != WF_DONE);
-    if (lane == 0 && alive) atomicAdd(B.counters + WFC_ALIVE + par, (unsigned)__popc(alive));
+    const int alive = __syncthreads_count(valid && state != WF_DONE);
+    if (threadIdx.x == 0 && alive) atomicAdd(B.counters + WFC_ALIVE + par, (unsigned)alive);
 }
 
 // ---- K9: trace the queue -----------------------------------------------------------------------------------
