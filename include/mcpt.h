@@ -172,6 +172,14 @@ MCPT_API int mcpt_trace_device(mcpt_ctx* ctx, const float* d_org_dir, int n, mcp
  * MCPT_NUM_CHUNKS sample chunks on this GPU.  width/height override the camera's when > 0. */
 MCPT_API int mcpt_render(mcpt_ctx* ctx, const mcpt_camera* cam, int width, int height, int spp, int mode,
                          int flags, float* rgb_out, mcpt_stats* stats);
+/* The output stage on the GPU (imshow + svpng, MTPC/MTPC.cpp:10-33, MTPC/svpng.inc:77-108): quantise a DEVICE image of
+ * height*width*3 floats and frame it as the same uncompressed PNG mcpt_write_png produces, byte for byte, into the HOST
+ * buffer png_out (capacity >= mcpt_png_size(width, height)). */
+MCPT_API int64_t mcpt_png_size(int width, int height);
+MCPT_API int mcpt_encode_png(mcpt_ctx* ctx, const float* d_rgb, int width, int height, uint8_t* png_out, int64_t capacity);
+/* Seam 3 + output stage: render, encode on the device, copy the PNG bytes (not the float image) to the host, write `file`. */
+MCPT_API int mcpt_render_png(mcpt_ctx* ctx, const mcpt_camera* cam, int width, int height, int spp, int mode, int flags,
+                             const char* file, mcpt_stats* stats);
 /* Multi-GPU building block: integrate only chunks [chunk_begin, chunk_end) of the spp samples and
  * leave their fixed-tree SUM (not mean) in the DEVICE buffer d_partial (height*width*3 floats). */
 MCPT_API int mcpt_render_chunks(mcpt_ctx* ctx, const mcpt_camera* cam, int width, int height, int spp,

@@ -70,6 +70,10 @@ SIGNATURES = {
     "mcpt_trace_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(Stats)]),
     "mcpt_render": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                               C.POINTER(Stats)]),
+    "mcpt_png_size": (C.c_int64, [C.c_int, C.c_int]),
+    "mcpt_encode_png": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int64]),
+    "mcpt_render_png": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p,
+                                  C.POINTER(Stats)]),
     "mcpt_render_chunks": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                      C.c_int, C.c_void_p, C.POINTER(Stats)]),
     "mcpt_sum_partials": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_void_p]),

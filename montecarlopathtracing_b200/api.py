@@ -155,7 +155,7 @@ class Context:
         self.last_stats = st
         return st
 
-    def render(self, camera, spp, width=0, height=0, mode=capi.MODE_MEGAKERNEL, flags=0, out=None):
+    def render(self, camera, spp, width=0, height=0, mode=capi.MODE_WAVEFRONT, flags=0, out=None):
         """generateImg: mean radiance image (H,W,3) float32 in a HOST buffer."""
         w = width if width > 0 else camera.width
         h = height if height > 0 else camera.height
@@ -166,8 +166,21 @@ class Context:
         self.last_stats = st
         return out
 
+    def encode_png(self, d_rgb_ptr, width, height):
+        """Device image (height*width*3 floats at d_rgb_ptr) -> PNG bytes (numpy uint8), encoded on the GPU."""
+        n = lib().mcpt_png_size(width, height)
+        out = np.empty(n, np.uint8)
+        check(lib().mcpt_encode_png(self._c, C.c_void_p(d_rgb_ptr), width, height, out.ctypes.data, n))
+        return out
+
+    def render_png(self, camera, spp, file, width=0, height=0, mode=capi.MODE_WAVEFRONT, flags=0):
+        st = capi.Stats()
+        check(lib().mcpt_render_png(self._c, C.byref(camera), width, height, spp, mode, flags, file.encode(), C.byref(st)))
+        self.last_stats = st
+        return st
+
     def render_chunks(self, camera, spp, chunk_begin, chunk_end, d_partial_ptr, width=0, height=0,
-                      mode=capi.MODE_MEGAKERNEL, flags=0):
+                      mode=capi.MODE_WAVEFRONT, flags=0):
         st = capi.Stats()
         check(lib().mcpt_render_chunks(self._c, C.byref(camera), width, height, spp, chunk_begin, chunk_end, mode, flags,
                                        C.c_void_p(d_partial_ptr), C.byref(st)))
@@ -188,3 +201,8 @@ def write_png(file, rgb):
     a = np.ascontiguousarray(rgb, dtype=np.float32)
     h, w = a.shape[0], a.shape[1]
     check(lib().mcpt_write_png(file.encode(), a.ctypes.data_as(C.POINTER(C.c_float)), w, h))
+
+
+def png_size(width, height):
+    """Size in bytes of the uncompressed PNG both the host and the device writer produce."""
+    return int(lib().mcpt_png_size(width, height))

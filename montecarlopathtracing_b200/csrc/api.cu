@@ -27,6 +27,7 @@ struct mcpt_ctx {
     float* d_planes = nullptr; size_t planes_cap = 0;   // scratch: sample-chunk planes
     float* d_image = nullptr; size_t image_cap = 0;     // scratch: reduced image
     float* d_dirs = nullptr; size_t dirs_cap = 0;       // scratch: primary ray directions (K7)
+    unsigned char* d_png = nullptr; size_t png_cap = 0; // scratch: device-encoded PNG (+64 B of sums/CRC in front)
     char* d_wf = nullptr; size_t wf_cap = 0;            // scratch: wavefront slot state + ray queue
     WfHost wfh;                                         // streams/events of the wavefront loop
     void* d_io = nullptr; size_t io_cap = 0;            // scratch: rays in / hits out of mcpt_trace
@@ -117,7 +118,7 @@ MCPT_API void mcpt_destroy(mcpt_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     free_scene(c);
-    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); c->wfh.destroy();
+    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); cudaFree(c->d_png); c->wfh.destroy();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->own_stream);
     delete c;
@@ -450,30 +451,81 @@ MCPT_API int mcpt_render_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, 
     return fill_kernel_times(c, st);
 }
 
-MCPT_API int mcpt_render(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, int spp, int mode, int flags, float* rgb_out,
-                         mcpt_stats* st) {
-    int rc = check_render_args(c, cam, width, height, spp);
-    if (rc) return rc;
-    if (!rgb_out) return fail_arg("mcpt_render: null output");
-    CU(cudaSetDevice(c->device));
+// Shared by mcpt_render and mcpt_render_png: the mean image is left in c->d_image; ev0..ev1 bracket the kernels.
+static int render_device(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, int spp, int mode, int flags, int* launches) {
     const size_t count = (size_t)width * height * 3;
     CU(grow(c->d_image, c->image_cap, sizeof(float) * count));
-    int launches = 0;
     CU(cudaEventRecord(c->ev0, c->stream));
-    rc = enqueue_chunks(c, cam, width, height, spp, 0, MCPT_NUM_CHUNKS, mode, flags, &launches);
+    const int rc = enqueue_chunks(c, cam, width, height, spp, 0, MCPT_NUM_CHUNKS, mode, flags, launches);
     if (rc) return rc;
     const int e = launch_sum_planes(c->d_planes, MCPT_NUM_CHUNKS, (long long)count, 1.0f / (float)spp, c->d_image, c->stream);
     if (e) return fail_cuda((cudaError_t)e, "sum_planes launch");
-    launches++;
+    (*launches)++;
     CU(cudaEventRecord(c->ev1, c->stream));
-    CU(cudaMemcpyAsync(rgb_out, c->d_image, sizeof(float) * count, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaStreamSynchronize(c->stream));
+    return MCPT_OK;
+}
+static int finish_render_stats(mcpt_ctx* c, mcpt_stats* st, int width, int height, int spp, int launches) {
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     unsigned long long cnt[4];
     CU(cudaMemcpy(cnt, c->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
     fill_stats(c, st, (double)width * height * (double)spp, cnt, ms, launches);
     return fill_kernel_times(c, st);
+}
+
+MCPT_API int mcpt_render(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, int spp, int mode, int flags, float* rgb_out,
+                         mcpt_stats* st) {
+    int rc = check_render_args(c, cam, width, height, spp);
+    if (rc) return rc;
+    if (!rgb_out) return fail_arg("mcpt_render: null output");
+    CU(cudaSetDevice(c->device));
+    int launches = 0;
+    rc = render_device(c, cam, width, height, spp, mode, flags, &launches);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(rgb_out, c->d_image, sizeof(float) * (size_t)width * height * 3, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return finish_render_stats(c, st, width, height, spp, launches);
+}
+
+MCPT_API int64_t mcpt_png_size(int width, int height) {
+    if (width <= 0 || height <= 0) return 0;
+    return (int64_t)png_encoded_size(width, height);
+}
+
+MCPT_API int mcpt_encode_png(mcpt_ctx* c, const float* d_rgb, int width, int height, uint8_t* png_out, int64_t capacity) {
+    if (!c || !d_rgb || !png_out || width <= 0 || height <= 0) return fail_arg("mcpt_encode_png: bad argument");
+    const size_t bytes = png_encoded_size(width, height);
+    if (capacity < (int64_t)bytes) return fail_arg("mcpt_encode_png: output buffer smaller than mcpt_png_size()");
+    CU(cudaSetDevice(c->device));
+    CU(grow(c->d_png, c->png_cap, bytes + 64));
+    const int e = launch_png_encode(d_rgb, width, height, c->d_png + 64, c->d_png, c->stream);   // first 64 B: scratch
+    if (e) return fail_cuda((cudaError_t)e, "png encode launch");
+    CU(cudaMemcpyAsync(png_out, c->d_png + 64, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return MCPT_OK;
+}
+
+MCPT_API int mcpt_render_png(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, int spp, int mode, int flags, const char* file,
+                             mcpt_stats* st) {
+    int rc = check_render_args(c, cam, width, height, spp);
+    if (rc) return rc;
+    if (!file) return fail_arg("mcpt_render_png: null file name");
+    CU(cudaSetDevice(c->device));
+    int launches = 0;
+    rc = render_device(c, cam, width, height, spp, mode, flags, &launches);
+    if (rc) return rc;
+    std::vector<uint8_t> png((size_t)mcpt_png_size(width, height));
+    rc = mcpt_encode_png(c, c->d_image, width, height, png.data(), (int64_t)png.size());   // synchronises the stream
+    if (rc) return rc;
+    launches += 4;
+    rc = finish_render_stats(c, st, width, height, spp, launches);
+    if (rc) return rc;
+    FILE* f = std::fopen(file, "wb");
+    if (!f) { mcpt_set_error((std::string("cannot open ") + file).c_str()); return MCPT_ERR_IO; }
+    bool ok = std::fwrite(png.data(), 1, png.size(), f) == png.size();
+    ok = (std::fclose(f) == 0) && ok;
+    if (!ok) { mcpt_set_error("short write"); return MCPT_ERR_IO; }
+    return MCPT_OK;
 }
 
 }  // extern "C"

@@ -27,4 +27,7 @@ struct WfHost {   // per-context host resources of the wavefront loop (created o
 int launch_wavefront(const RenderParams& P, int flags, void* d_scratch, WfHost& H, cudaStream_t stream, int* launches);
 // K12: out[i] = scale * fixed pairwise tree sum over n planes (n in {1,2,4,8}).
 int launch_sum_planes(const float* d_planes, int n, long long count, float scale, float* d_out, cudaStream_t stream);
+// K13-K15 (png_device.cu): quantise + frame the image as an uncompressed PNG on the device.
+size_t png_encoded_size(int w, int h);
+int launch_png_encode(const float* d_rgb, int w, int h, unsigned char* d_png, void* d_scratch32, cudaStream_t stream);
 }  // namespace mcpt

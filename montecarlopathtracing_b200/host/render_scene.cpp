@@ -14,18 +14,17 @@ int render_to_png(const std::string& path, const std::string& name, int spp, con
     if (rc) return rc;
     mcpt_ctx* ctx = nullptr;
     const mcpt_camera* cam = mcpt_scene_get_camera(hs);
-    std::vector<float> rgb(size_t(cam->width) * cam->height * 3);
     mcpt_stats st{};
     float build_ms = 0;
     rc = mcpt_create(device, &ctx);
     if (!rc) rc = mcpt_upload_scene(ctx, mcpt_scene_get_desc(hs));
     if (!rc) rc = mcpt_build_bvh(ctx, &build_ms);
-    if (!rc) rc = mcpt_render(ctx, cam, 0, 0, spp, MCPT_MODE_MEGAKERNEL, 0, rgb.data(), &st);
+    const std::string file = out_dir + name + "-SPP" + std::to_string(spp) + ".png";  // MTPC/MTPC.cpp:19-20,64-65
+    // integrator + imshow/svpng on the device: only the finished PNG crosses PCIe
+    if (!rc) rc = mcpt_render_png(ctx, cam, 0, 0, spp, MCPT_MODE_WAVEFRONT, 0, file.c_str(), &st);
     if (!rc) {
         std::printf("Phase 1 (GPU LBVH build) = %.3f ms\nPhase 2 (path tracing) = %.3f ms, %.1f Msamples/s, %.1f Mrays/s\n",
                     build_ms, st.render_ms, st.samples / st.render_ms * 1e-3, st.rays / st.render_ms * 1e-3);
-        const std::string file = out_dir + name + "-SPP" + std::to_string(spp) + ".png";  // MTPC/MTPC.cpp:19-20,64-65
-        rc = mcpt_write_png(file.c_str(), rgb.data(), cam->width, cam->height);
     }
     if (ctx) mcpt_destroy(ctx);
     mcpt_scene_free(hs);

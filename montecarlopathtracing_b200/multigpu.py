@@ -40,7 +40,7 @@ def render_split(render_partial, sum_partials, spp, rank=0, world=1, group=None)
     return sum_partials(torch.cat(gathered), world, 1.0 / spp)
 
 
-def gpu_backend(ctx, camera, spp, width, height, mode=0, flags=0):
+def gpu_backend(ctx, camera, spp, width, height, mode=1, flags=0):
     """Binds render_partial / sum_partials to a CUDA Context; tensors are torch CUDA tensors (device memory only)."""
     w = width if width > 0 else camera.width
     h = height if height > 0 else camera.height

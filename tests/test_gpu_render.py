@@ -27,7 +27,7 @@ def test_pixelwise_vs_oracle_same_random_numbers(gpu_ctx, oracle, scenes, name, 
     s = scenes[name]
     _load(gpu_ctx, s)
     gpu_ctx.set_seed(1234)
-    img = gpu_ctx.render(s.camera, spp, w, h)
+    img = gpu_ctx.render(s.camera, spp, w, h, mode=M.MODE_MEGAKERNEL)
     ref, counts = oracle.OracleScene(s.desc).render(s.camera, spp, w, h, seed=1234)
     assert np.all(np.isfinite(img))
     close = np.abs(img - ref) <= 2e-3 * np.abs(ref) + 1e-4
@@ -190,3 +190,36 @@ def test_wavefront_chunk_ranges_are_gpu_count_independent(gpu_ctx, scenes):
         out = sum_partials(torch.cat(parts), R, 1.0 / spp)
         torch.cuda.synchronize()
         assert np.array_equal(out.cpu().numpy().reshape(h, w, 3), base), "R=%d differs" % R
+
+
+@pytest.mark.parametrize("h,w", [(1, 1), (37, 301), (270, 480), (1080, 1920)])
+def test_device_png_stage_is_byte_identical_to_the_host_writer(gpu_ctx, tmp_path, h, w):
+    """imshow + svpng on the GPU (K13-K15): quantisation (uchar)clamp(v*255,0,255) incl. negatives, > 1 and NaN, stored
+    deflate blocks (several per image above 65535 raw bytes), Adler-32 and both CRC-32s — the same bytes as
+    mcpt_write_png (whose output test_host.py checks against the reference's rule and a PNG decoder)."""
+    import torch
+    rng = np.random.default_rng(h * 10007 + w)
+    img = rng.uniform(-0.2, 1.4, size=(h, w, 3)).astype(np.float32)
+    img.reshape(-1)[::97] = np.nan
+    img.reshape(-1)[5::131] = 50.0
+    f = str(tmp_path / "host.png")
+    M.write_png(f, img)
+    want = np.fromfile(f, np.uint8)
+    d = torch.from_numpy(img).cuda()
+    got = gpu_ctx.encode_png(d.data_ptr(), w, h)
+    assert len(got) == len(want) == M.png_size(w, h)
+    assert np.array_equal(got, want), "first differing byte at %d" % int(np.nonzero(got != want)[0][0])
+
+
+def test_render_png_equals_render_then_write(gpu_ctx, scenes, tmp_path):
+    from PIL import Image
+    s = scenes["veach-mis"]
+    _load(gpu_ctx, s)
+    gpu_ctx.set_seed(3)
+    f = str(tmp_path / "dev.png")
+    st = gpu_ctx.render_png(s.camera, 4, f, 300, 225)
+    img = gpu_ctx.render(s.camera, 4, 300, 225)
+    g = str(tmp_path / "host.png")
+    M.write_png(g, img)
+    assert open(f, "rb").read() == open(g, "rb").read()
+    assert st.samples == 300 * 225 * 4 and np.asarray(Image.open(f)).shape == (225, 300, 3)

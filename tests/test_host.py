@@ -128,3 +128,4 @@ def test_png_quantisation_matches_imshow(tmp_path):
     assert np.array_equal(got, want)
     from PIL import Image
     assert np.array_equal(np.asarray(Image.open(f)), want)
+    assert os.path.getsize(f) == M.png_size(301, 37)
