@@ -112,6 +112,7 @@ enum { MCPT_FLAG_COUNT = 1,            /* count node visits / triangle tests (sl
 /* ---- host side: the kept C++ shell (loaders, render_scene, PNG) ---------------------------- */
 
 typedef struct mcpt_host_scene mcpt_host_scene;
+typedef struct mcpt_ctx mcpt_ctx;
 
 /* Parse <path><name>.{mtl,obj,camera} with the reference's grammar
  * (MTPC/sceneManagement.cpp:17-274; CRLF-safe) and flatten to mcpt_scene_desc.  Textures are read
@@ -121,6 +122,8 @@ MCPT_API int mcpt_scene_load(const char* path, const char* name, mcpt_host_scene
 MCPT_API const mcpt_scene_desc* mcpt_scene_get_desc(const mcpt_host_scene* s);
 MCPT_API const mcpt_camera* mcpt_scene_get_camera(const mcpt_host_scene* s);
 MCPT_API void mcpt_scene_free(mcpt_host_scene* s);
+/* Name of material i as newmtl spelled it (NULL if out of range); valid until mcpt_scene_free. */
+MCPT_API const char* mcpt_scene_get_material_name(const mcpt_host_scene* s, int32_t i);
 
 /* render_scene(path, filename, spp) of MTPC/MTPC.cpp:35-68 on cuda device `device`:
  * load -> upload -> build -> render -> quantise -> <out_dir><name>-SPP<spp>.png
@@ -133,8 +136,6 @@ MCPT_API int mcpt_write_png(const char* file, const float* rgb, int width, int h
 
 /* ---- device side --------------------------------------------------------------------------- */
 
-typedef struct mcpt_ctx mcpt_ctx;
-
 MCPT_API const char* mcpt_last_error(void);
 MCPT_API int mcpt_create(int device, mcpt_ctx** out);
 MCPT_API void mcpt_destroy(mcpt_ctx* ctx);
@@ -145,6 +146,24 @@ MCPT_API int mcpt_set_seed(mcpt_ctx* ctx, uint64_t seed);
 
 /* H2D copy of the flattened scene; precomputes per-light area CDFs (MTPC/pathTracing.cpp:177-184). */
 MCPT_API int mcpt_upload_scene(mcpt_ctx* ctx, const mcpt_scene_desc* scene);
+
+/* Scene ingest on the GPU: scene_data::read_obj (MTPC/sceneManagement.cpp:76-189) as kernels over
+ * the OBJ file's bytes (HOST buffer obj_text, copied H2D once): statements counted and indexed by a scan, numbers converted
+ * exactly as atof/strtod rounds them, faces range-checked and flattened straight into the device arrays mcpt_upload_scene
+ * would have filled — bit-identical to mcpt_scene_load + mcpt_upload_scene, without the per-face FP64 arrays ever existing
+ * on the host.  `tables` supplies materials / textures / lights (its per-face pointers and n_faces are ignored);
+ * material_names[n_materials] resolves usemtl.  Errors (MCPT_ERR_IO): non-triangle face, unknown material, index out of
+ * range — the first offending line, as the sequential reader meets it — and numbers atof would read but this parser
+ * does not (hex floats, inf/nan, > 40 significant digits).  ms_out (may be NULL) = device time incl. the H2D copy. */
+MCPT_API int mcpt_ingest_obj(mcpt_ctx* ctx, const char* obj_text, int64_t n_bytes, const mcpt_scene_desc* tables,
+                             const char* const* material_names, float* ms_out);
+/* read_scene (MTPC/sceneManagement.cpp:264-274) with the OBJ on the GPU: <path><name>.mtl and .camera are parsed on the
+ * host (a few lines each), the .obj by mcpt_ingest_obj.  Leaves the context as mcpt_upload_scene would. */
+MCPT_API int mcpt_scene_load_gpu(mcpt_ctx* ctx, const char* path, const char* name, mcpt_camera* camera_out, float* ingest_ms_out);
+/* Parity hooks for the ingest: face count of the resident scene (negative = error) and its flattened arrays
+ * (9/9/6 doubles and one int32 per face, HOST buffers; any pointer may be NULL). */
+MCPT_API int64_t mcpt_scene_face_count(mcpt_ctx* ctx);
+MCPT_API int mcpt_get_scene_arrays(mcpt_ctx* ctx, double* pos, double* nrm, double* uv, int32_t* mat_id);
 
 /* Seam 1. Morton codes (bit-exact with MTPC/morton code.cpp:3-32) -> CUB radix sort of (code, face)
  * -> Karras radix tree -> bottom-up AABB refit -> traversal layout.  ms_out (may be NULL) = device time. */

@@ -54,6 +54,11 @@ SIGNATURES = {
     "mcpt_scene_get_desc": (C.POINTER(SceneDesc), [C.c_void_p]),
     "mcpt_scene_get_camera": (C.POINTER(Camera), [C.c_void_p]),
     "mcpt_scene_free": (None, [C.c_void_p]),
+    "mcpt_scene_get_material_name": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "mcpt_ingest_obj": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(SceneDesc), C.POINTER(C.c_char_p), C.POINTER(C.c_float)]),
+    "mcpt_scene_load_gpu": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(Camera), C.POINTER(C.c_float)]),
+    "mcpt_scene_face_count": (C.c_int64, [C.c_void_p]),
+    "mcpt_get_scene_arrays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "mcpt_render_scene": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int]),
     "mcpt_write_png": (C.c_int, [C.c_char_p, C.POINTER(C.c_float), C.c_int, C.c_int]),
     "mcpt_last_error": (C.c_char_p, []),

@@ -37,6 +37,7 @@ class HostScene:
         self.materials = [d.materials[i] for i in range(d.n_materials)]
         self.lights = [d.lights[i] for i in range(d.n_lights)]
         self.textures = [d.textures[i] for i in range(d.n_textures)]
+        self.material_names = [lib().mcpt_scene_get_material_name(self._h, i).decode() for i in range(d.n_materials)]
 
     def close(self):
         if self._h:
@@ -112,6 +113,37 @@ class Context:
             desc = desc.desc
         check(lib().mcpt_upload_scene(self._c, C.byref(desc)))
         self.n_faces = desc.n_faces
+
+    def ingest_obj(self, obj_text, tables, material_names=None):
+        """read_obj on the GPU: obj_text = the .obj file's bytes; tables = HostScene or SceneDesc giving materials, textures
+        and lights; material_names resolves usemtl (taken from a HostScene).  Returns the device time in ms."""
+        if isinstance(tables, HostScene):
+            material_names = tables.material_names if material_names is None else material_names
+            tables = tables.desc
+        names = (C.c_char_p * max(len(material_names), 1))(*[n.encode() for n in material_names])
+        buf = np.frombuffer(obj_text, dtype=np.uint8)
+        ms = C.c_float()
+        self.n_faces = 0
+        check(lib().mcpt_ingest_obj(self._c, C.c_void_p(buf.ctypes.data), buf.size, C.byref(tables), names, C.byref(ms)))
+        self.n_faces = int(lib().mcpt_scene_face_count(self._c))
+        return ms.value
+
+    def load_scene_gpu(self, path, name):
+        """read_scene with the OBJ parsed on the GPU.  Returns (camera, ingest_ms)."""
+        cam, ms = capi.Camera(), C.c_float()
+        self.n_faces = 0
+        check(lib().mcpt_scene_load_gpu(self._c, path.encode(), name.encode(), C.byref(cam), C.byref(ms)))
+        self.n_faces = int(lib().mcpt_scene_face_count(self._c))
+        return cam, ms.value
+
+    def get_scene_arrays(self):
+        """The flattened scene resident on the device: pos (n,3,3), nrm (n,3,3), uv (n,3,2) float64, mat_id (n,) int32."""
+        n = int(lib().mcpt_scene_face_count(self._c))
+        if n < 0:
+            check(n)
+        pos, nrm, uv, mat = np.empty((n, 3, 3)), np.empty((n, 3, 3)), np.empty((n, 3, 2)), np.empty(n, np.int32)
+        check(lib().mcpt_get_scene_arrays(self._c, pos.ctypes.data, nrm.ctypes.data, uv.ctypes.data, mat.ctypes.data))
+        return pos, nrm, uv, mat
 
     def build_bvh(self):
         ms = C.c_float()

@@ -21,7 +21,7 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-ccbin", CXX, "-Xcompiler", "-fPIC,-fvisibility=hidden"]
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall"]
 
-CU_SOURCES = {"lbvh.cu": ["--fmad=false"], "ploc.cu": [], "render.cu": [], "wavefront.cu": [], "png_device.cu": [], "api.cu": []}
+CU_SOURCES = {"lbvh.cu": ["--fmad=false"], "ploc.cu": [], "render.cu": [], "wavefront.cu": [], "png_device.cu": [], "obj_ingest.cu": [], "api.cu": []}
 CPP_SOURCES = ["scene_loader.cpp", "png_writer.cpp", "render_scene.cpp", "mcpt_error.cpp"]
 
 

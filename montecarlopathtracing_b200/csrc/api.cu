@@ -8,6 +8,7 @@
 #include <vector>
 #include "lbvh.h"
 #include "render.h"
+#include "obj_ingest.h"
 
 void mcpt_set_error(const char* msg);  // host/mcpt_error.cpp
 
@@ -31,6 +32,8 @@ struct mcpt_ctx {
     char* d_wf = nullptr; size_t wf_cap = 0;            // scratch: wavefront slot state + ray queue
     WfHost wfh;                                         // streams/events of the wavefront loop
     void* d_io = nullptr; size_t io_cap = 0;            // scratch: rays in / hits out of mcpt_trace
+    char* d_text = nullptr; size_t text_cap = 0;        // scratch: OBJ text of mcpt_ingest_obj
+    int last_ingest_launches = 0;
     float last_build_ms = 0.f;
     bool scene_loaded = false;
 };
@@ -86,6 +89,107 @@ DeviceScene device_scene(const mcpt_ctx* c) {
     d.lights = c->d_lights; d.light_tris = c->d_light_tris; d.light_cdf = c->d_light_cdf;
     return d;
 }
+
+int check_tables(const mcpt_scene_desc* d, const char* who) {
+    auto bad = [&](const char* what) { return fail_arg((std::string(who) + ": " + what).c_str()); };
+    if (d->n_materials <= 0 || !d->materials) return bad("no materials");
+    for (int l = 0; l < d->n_lights; l++)
+        if (d->lights[l].mat_id < 0 || d->lights[l].mat_id >= d->n_materials) return bad("light mat_id out of range");
+    for (int m = 0; m < d->n_materials; m++)
+        if (d->materials[m].tex_id >= d->n_textures) return bad("tex_id out of range");
+    for (int i = 0; i < d->n_textures; i++)
+        if (d->textures[i].height <= 0 || d->textures[i].width <= 0 || !d->textures[i].bgr) return bad("bad texture");
+    return MCPT_OK;
+}
+
+// every per-face device array of a scene of n faces (geometry, build scratch, trees)
+int alloc_scene(mcpt_ctx* c, int n) {
+    SceneBuffers& s = c->sb;
+    s.n_faces = n;
+    const size_t N = (size_t)n;
+    CU(dev_alloc(s.pos, 9 * N)); CU(dev_alloc(s.nrm, 9 * N)); CU(dev_alloc(s.uv, 6 * N)); CU(dev_alloc(s.mat_id, N));
+    CU(dev_alloc(s.codes_obj, N)); CU(dev_alloc(s.codes_sorted, N)); CU(dev_alloc(s.iota, N)); CU(dev_alloc(s.leaf_face, N));
+    CU(dev_alloc(s.leaf_parent, N)); CU(dev_alloc(s.flags, N)); CU(dev_alloc(s.nodes, N)); CU(dev_alloc(s.tri, N));
+    CU(dev_alloc(s.shade, N)); CU(dev_alloc(s.root_box, 6)); CU(dev_alloc(s.qnodes, N)); CU(dev_alloc(s.qgrid, 1));
+    CU(dev_alloc(s.nodes2, N)); CU(dev_alloc(s.cl_lo[0], N)); CU(dev_alloc(s.cl_lo[1], N)); CU(dev_alloc(s.cl_hi[0], N)); CU(dev_alloc(s.cl_hi[1], N));
+    CU(dev_alloc(s.ploc_nn, N)); CU(dev_alloc(s.ploc_flag, N)); CU(dev_alloc(s.ploc_scan, N));
+    s.ploc_temp_bytes = ploc_scan_temp_bytes(n);
+    CU(cudaMalloc(&s.ploc_temp, s.ploc_temp_bytes ? s.ploc_temp_bytes : 1));
+    CU(cudaMalloc(&s.ploc_state, 64));
+    { const char* v = getenv("MCPT_BVH"); s.use_ploc = !(v && std::strcmp(v, "lbvh") == 0); }
+    s.cub_temp_bytes = lbvh_sort_temp_bytes(n);
+    CU(cudaMalloc(&s.cub_temp, s.cub_temp_bytes ? s.cub_temp_bytes : 1));
+    return MCPT_OK;
+}
+
+// materials, textures and lights; lpos/lnrm[l] = the faces of light l's material in OBJ order (9 doubles each)
+int upload_tables(mcpt_ctx* c, const mcpt_scene_desc* d, const std::vector<std::vector<double>>& lpos,
+                  const std::vector<std::vector<double>>& lnrm) {
+    cudaStream_t st = c->stream;
+    // materials: light_id = light_map lookup (the last "mtlname" line naming the material wins, sceneManagement.cpp:256)
+    std::vector<DMaterial> mats(d->n_materials);
+    for (int m = 0; m < d->n_materials; m++) {
+        const mcpt_material& src = d->materials[m];
+        DMaterial& t = mats[m];
+        for (int k = 0; k < 3; k++) { t.kd[k] = (float)src.kd[k]; t.ks[k] = (float)src.ks[k]; }
+        t.kd_norm = (float)std::sqrt(src.kd[0] * src.kd[0] + src.kd[1] * src.kd[1] + src.kd[2] * src.kd[2]);
+        t.ks_norm = (float)std::sqrt(src.ks[0] * src.ks[0] + src.ks[1] * src.ks[1] + src.ks[2] * src.ks[2]);
+        t.Ns = (float)src.Ns; t.Ni = (float)src.Ni; t.tex_id = src.tex_id; t.light_id = -1;
+    }
+    for (int l = 0; l < d->n_lights; l++) mats[d->lights[l].mat_id].light_id = l;
+    // textures, packed back to back
+    std::vector<DTexture> texs(d->n_textures);
+    std::vector<unsigned char> tex_bytes;
+    for (int i = 0; i < d->n_textures; i++) {
+        const mcpt_texture& t = d->textures[i];
+        texs[i].height = t.height; texs[i].width = t.width; texs[i].offset = tex_bytes.size();
+        tex_bytes.insert(tex_bytes.end(), t.bgr, t.bgr + (size_t)t.height * t.width * 3);
+    }
+    // lights: area CDF over the light material's faces in OBJ order (MTPC/pathTracing.cpp:177-184), built once
+    std::vector<DLight> lights(d->n_lights);
+    std::vector<LightTri> ltris;
+    std::vector<float> cdf;
+    std::vector<double> areas(d->n_lights, 0.0);
+    for (int l = 0; l < d->n_lights; l++) {
+        DLight& L = lights[l];
+        L.mat_id = d->lights[l].mat_id; L.first = (int)ltris.size(); L.count = 0;
+        for (int k = 0; k < 3; k++) L.radiance[k] = (float)d->lights[l].radiance[k];
+        double total = 0;
+        for (size_t j = 0; j < lpos[l].size() / 9; j++) {
+            const double* p = &lpos[l][9 * j]; const double* q = &lnrm[l][9 * j];
+            total += face_area(p);
+            cdf.push_back((float)total);
+            LightTri t;
+            t.p0n0x = make_float4((float)p[0], (float)p[1], (float)p[2], (float)q[0]);
+            t.p1n0y = make_float4((float)p[3], (float)p[4], (float)p[5], (float)q[1]);
+            t.p2n0z = make_float4((float)p[6], (float)p[7], (float)p[8], (float)q[2]);
+            t.n1n2x = make_float4((float)q[3], (float)q[4], (float)q[5], (float)q[6]);
+            t.n2yz = make_float4((float)q[7], (float)q[8], 0.f, 0.f);
+            ltris.push_back(t);
+            L.count++;
+        }
+        areas[l] = total; L.area = (float)total;
+    }
+    c->area0 = d->n_lights > 0 ? (float)areas[0] : 0.f;
+    for (int l = 0; l < d->n_lights; l++) {   // entries reachable by rnd <= area0 (quirk Q6): bounds the binary search
+        DLight& L = lights[l];
+        int m = 0;
+        while (m < L.count && !(cdf[L.first + m] > c->area0)) m++;
+        L.n_search = m < L.count ? m + 1 : L.count;
+    }
+    c->n_materials = d->n_materials; c->n_textures = d->n_textures; c->n_lights = d->n_lights;
+    CU(dev_alloc(c->d_materials, mats.size())); CU(dev_alloc(c->d_textures, texs.size())); CU(dev_alloc(c->d_tex_bytes, tex_bytes.size()));
+    CU(dev_alloc(c->d_lights, lights.size())); CU(dev_alloc(c->d_light_tris, ltris.size())); CU(dev_alloc(c->d_light_cdf, cdf.size()));
+    CU(cudaMemcpyAsync(c->d_materials, mats.data(), sizeof(DMaterial) * mats.size(), cudaMemcpyHostToDevice, st));
+    if (!texs.empty()) CU(cudaMemcpyAsync(c->d_textures, texs.data(), sizeof(DTexture) * texs.size(), cudaMemcpyHostToDevice, st));
+    if (!tex_bytes.empty()) CU(cudaMemcpyAsync(c->d_tex_bytes, tex_bytes.data(), tex_bytes.size(), cudaMemcpyHostToDevice, st));
+    if (!lights.empty()) CU(cudaMemcpyAsync(c->d_lights, lights.data(), sizeof(DLight) * lights.size(), cudaMemcpyHostToDevice, st));
+    if (!ltris.empty()) CU(cudaMemcpyAsync(c->d_light_tris, ltris.data(), sizeof(LightTri) * ltris.size(), cudaMemcpyHostToDevice, st));
+    if (!cdf.empty()) CU(cudaMemcpyAsync(c->d_light_cdf, cdf.data(), sizeof(float) * cdf.size(), cudaMemcpyHostToDevice, st));
+    CU(cudaStreamSynchronize(st));  // the staging vectors die here
+    c->scene_loaded = true;
+    return MCPT_OK;
+}
 }  // namespace
 
 extern "C" {
@@ -118,7 +222,7 @@ MCPT_API void mcpt_destroy(mcpt_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     free_scene(c);
-    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); cudaFree(c->d_png); c->wfh.destroy();
+    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); cudaFree(c->d_png); cudaFree(c->d_text); c->wfh.destroy();
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->own_stream);
     delete c;
@@ -138,101 +242,122 @@ MCPT_API int mcpt_set_seed(mcpt_ctx* c, uint64_t seed) {
 MCPT_API int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     if (!c || !d) return fail_arg("mcpt_upload_scene: null argument");
     if (d->n_faces <= 0 || !d->pos || !d->nrm || !d->uv || !d->mat_id) return fail_arg("mcpt_upload_scene: empty scene");
-    if (d->n_materials <= 0 || !d->materials) return fail_arg("mcpt_upload_scene: no materials");
+    if (int rc = check_tables(d, "mcpt_upload_scene")) return rc;
     const int n = d->n_faces;
     for (int i = 0; i < n; i++)
         if (d->mat_id[i] < 0 || d->mat_id[i] >= d->n_materials) return fail_arg("mcpt_upload_scene: mat_id out of range");
-    for (int l = 0; l < d->n_lights; l++)
-        if (d->lights[l].mat_id < 0 || d->lights[l].mat_id >= d->n_materials) return fail_arg("mcpt_upload_scene: light mat_id out of range");
-    for (int m = 0; m < d->n_materials; m++)
-        if (d->materials[m].tex_id >= d->n_textures) return fail_arg("mcpt_upload_scene: tex_id out of range");
     CU(cudaSetDevice(c->device));
     free_scene(c);
+    if (int rc = alloc_scene(c, n)) return rc;
     SceneBuffers& s = c->sb;
-    s.n_faces = n;
     const size_t N = (size_t)n;
-    CU(dev_alloc(s.pos, 9 * N)); CU(dev_alloc(s.nrm, 9 * N)); CU(dev_alloc(s.uv, 6 * N)); CU(dev_alloc(s.mat_id, N));
-    CU(dev_alloc(s.codes_obj, N)); CU(dev_alloc(s.codes_sorted, N)); CU(dev_alloc(s.iota, N)); CU(dev_alloc(s.leaf_face, N));
-    CU(dev_alloc(s.leaf_parent, N)); CU(dev_alloc(s.flags, N)); CU(dev_alloc(s.nodes, N)); CU(dev_alloc(s.tri, N));
-    CU(dev_alloc(s.shade, N)); CU(dev_alloc(s.root_box, 6)); CU(dev_alloc(s.qnodes, N)); CU(dev_alloc(s.qgrid, 1));
-    CU(dev_alloc(s.nodes2, N)); CU(dev_alloc(s.cl_lo[0], N)); CU(dev_alloc(s.cl_lo[1], N)); CU(dev_alloc(s.cl_hi[0], N)); CU(dev_alloc(s.cl_hi[1], N));
-    CU(dev_alloc(s.ploc_nn, N)); CU(dev_alloc(s.ploc_flag, N)); CU(dev_alloc(s.ploc_scan, N));
-    s.ploc_temp_bytes = ploc_scan_temp_bytes(n);
-    CU(cudaMalloc(&s.ploc_temp, s.ploc_temp_bytes ? s.ploc_temp_bytes : 1));
-    CU(cudaMalloc(&s.ploc_state, 64));
-    { const char* v = getenv("MCPT_BVH"); s.use_ploc = !(v && std::strcmp(v, "lbvh") == 0); }
-    s.cub_temp_bytes = lbvh_sort_temp_bytes(n);
-    CU(cudaMalloc(&s.cub_temp, s.cub_temp_bytes ? s.cub_temp_bytes : 1));
     cudaStream_t st = c->stream;
     CU(cudaMemcpyAsync(s.pos, d->pos, 72 * N, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s.nrm, d->nrm, 72 * N, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s.uv, d->uv, 48 * N, cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(s.mat_id, d->mat_id, 4 * N, cudaMemcpyHostToDevice, st));
-
-    // materials: light_id = light_map lookup (the last "mtlname" line naming the material wins, sceneManagement.cpp:256)
-    std::vector<DMaterial> mats(d->n_materials);
-    for (int m = 0; m < d->n_materials; m++) {
-        const mcpt_material& src = d->materials[m];
-        DMaterial& t = mats[m];
-        for (int k = 0; k < 3; k++) { t.kd[k] = (float)src.kd[k]; t.ks[k] = (float)src.ks[k]; }
-        t.kd_norm = (float)std::sqrt(src.kd[0] * src.kd[0] + src.kd[1] * src.kd[1] + src.kd[2] * src.kd[2]);
-        t.ks_norm = (float)std::sqrt(src.ks[0] * src.ks[0] + src.ks[1] * src.ks[1] + src.ks[2] * src.ks[2]);
-        t.Ns = (float)src.Ns; t.Ni = (float)src.Ni; t.tex_id = src.tex_id; t.light_id = -1;
-    }
-    for (int l = 0; l < d->n_lights; l++) mats[d->lights[l].mat_id].light_id = l;
-    // textures, packed back to back
-    std::vector<DTexture> texs(d->n_textures);
-    std::vector<unsigned char> tex_bytes;
-    for (int i = 0; i < d->n_textures; i++) {
-        const mcpt_texture& t = d->textures[i];
-        if (t.height <= 0 || t.width <= 0 || !t.bgr) return fail_arg("mcpt_upload_scene: bad texture");
-        texs[i].height = t.height; texs[i].width = t.width; texs[i].offset = tex_bytes.size();
-        tex_bytes.insert(tex_bytes.end(), t.bgr, t.bgr + (size_t)t.height * t.width * 3);
-    }
-    // lights: area CDF over the light material's faces in OBJ order (MTPC/pathTracing.cpp:177-184), built once
-    std::vector<DLight> lights(d->n_lights);
-    std::vector<LightTri> ltris;
-    std::vector<float> cdf;
-    std::vector<double> areas(d->n_lights, 0.0);
-    for (int l = 0; l < d->n_lights; l++) {
-        DLight& L = lights[l];
-        L.mat_id = d->lights[l].mat_id; L.first = (int)ltris.size(); L.count = 0;
-        for (int k = 0; k < 3; k++) L.radiance[k] = (float)d->lights[l].radiance[k];
-        double total = 0;
+    // faces of every light's material, OBJ order
+    std::vector<std::vector<double>> lpos(d->n_lights), lnrm(d->n_lights);
+    for (int l = 0; l < d->n_lights; l++)
         for (int i = 0; i < n; i++) {
-            if (d->mat_id[i] != L.mat_id) continue;
-            const double* p = d->pos + 9 * (size_t)i; const double* q = d->nrm + 9 * (size_t)i;
-            total += face_area(p);
-            cdf.push_back((float)total);
-            LightTri t;
-            t.p0n0x = make_float4((float)p[0], (float)p[1], (float)p[2], (float)q[0]);
-            t.p1n0y = make_float4((float)p[3], (float)p[4], (float)p[5], (float)q[1]);
-            t.p2n0z = make_float4((float)p[6], (float)p[7], (float)p[8], (float)q[2]);
-            t.n1n2x = make_float4((float)q[3], (float)q[4], (float)q[5], (float)q[6]);
-            t.n2yz = make_float4((float)q[7], (float)q[8], 0.f, 0.f);
-            ltris.push_back(t);
-            L.count++;
+            if (d->mat_id[i] != d->lights[l].mat_id) continue;
+            lpos[l].insert(lpos[l].end(), d->pos + 9 * (size_t)i, d->pos + 9 * (size_t)i + 9);
+            lnrm[l].insert(lnrm[l].end(), d->nrm + 9 * (size_t)i, d->nrm + 9 * (size_t)i + 9);
         }
-        areas[l] = total; L.area = (float)total;
+    return upload_tables(c, d, lpos, lnrm);
+}
+
+/* Scene ingest on the GPU: see include/mcpt.h and csrc/obj_ingest.cu. */
+MCPT_API int mcpt_ingest_obj(mcpt_ctx* c, const char* text, int64_t n_bytes, const mcpt_scene_desc* d, const char* const* names,
+                             float* ms_out) {
+    if (!c || !text || !d || !names) return fail_arg("mcpt_ingest_obj: null argument");
+    if (n_bytes <= 0 || n_bytes >= (int64_t)0xFFFFFF00ll) return fail_arg("mcpt_ingest_obj: text must be 1 byte .. 4 GiB");
+    if (int rc = check_tables(d, "mcpt_ingest_obj")) return rc;
+    CU(cudaSetDevice(c->device));
+    free_scene(c);
+    cudaStream_t st = c->stream;
+    CU(cudaEventRecord(c->ev0, st));
+    CU(grow(c->d_text, c->text_cap, (size_t)n_bytes));
+    CU(cudaMemcpyAsync(c->d_text, text, (size_t)n_bytes, cudaMemcpyHostToDevice, st));
+    ObjIngest g;
+    g.d_text = c->d_text; g.n_bytes = (unsigned)n_bytes;
+    struct Guard { ObjIngest& g; ~Guard() { obj_ingest_free(g); } } guard{g};
+    int e = obj_ingest_parse(g, st);
+    if (e) return fail_cuda((cudaError_t)e, "obj_ingest_parse");
+    auto obj_error = [&](unsigned long long w) {
+        static const char* what[] = {"", "only triangles are supported (as in the reference)", "face uses unknown material",
+                                     "face index out of range", "number not readable the way atof reads it (hex / inf / nan / > 40 digits)"};
+        const unsigned code = (unsigned)(w & 0xFF);
+        std::string m = std::string("obj: ") + what[code < 5 ? code : 0] + " (line at byte offset " + std::to_string(w >> 8) + ")";
+        mcpt_set_error(m.c_str());
+        return (int)MCPT_ERR_IO;
+    };
+    if (g.n_f == 0) {                                   // errors wait for stage 2: an unknown material on an earlier line comes first
+        if (g.h_status[0] != ~0ull) return obj_error(g.h_status[0]);
+        mcpt_set_error("obj: no faces");
+        return MCPT_ERR_IO;
     }
-    c->area0 = d->n_lights > 0 ? (float)areas[0] : 0.f;
-    for (int l = 0; l < d->n_lights; l++) {   // entries reachable by rnd <= area0 (quirk Q6): bounds the binary search
-        DLight& L = lights[l];
-        int m = 0;
-        while (m < L.count && !(cdf[L.first + m] > c->area0)) m++;
-        L.n_search = m < L.count ? m + 1 : L.count;
+    std::vector<std::string> um_names;
+    e = obj_ingest_names(g, um_names, st);
+    if (e) return fail_cuda((cudaError_t)e, "obj_ingest_names");
+    std::vector<int> um_mat(um_names.size(), -1);
+    for (size_t i = 0; i < um_names.size(); i++)
+        for (int m = 0; m < d->n_materials; m++)
+            if (names[m] && um_names[i] == names[m]) um_mat[i] = m;   // a repeated newmtl name keeps one entry (scene_loader.cpp)
+    if (int rc = alloc_scene(c, (int)g.n_f)) return rc;
+    SceneBuffers& s = c->sb;
+    e = obj_ingest_flatten(g, um_mat.data(), s.pos, s.nrm, s.uv, s.mat_id, st);
+    if (e) return fail_cuda((cudaError_t)e, "obj_ingest_flatten");
+    if (g.h_status[0] != ~0ull) { free_scene(c); return obj_error(g.h_status[0]); }
+    // light faces: material ids back to the host (4 B per face), index lists per light, one gather per light
+    const int n = (int)g.n_f;
+    std::vector<int> mat((size_t)n);
+    CU(cudaMemcpyAsync(mat.data(), s.mat_id, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    std::vector<std::vector<double>> lpos(d->n_lights), lnrm(d->n_lights);
+    for (int l = 0; l < d->n_lights; l++) {
+        std::vector<int> idx;
+        for (int i = 0; i < n; i++) if (mat[i] == d->lights[l].mat_id) idx.push_back(i);
+        if (idx.empty()) continue;
+        int* d_idx = nullptr; double* d_out = nullptr;
+        CU(dev_alloc(d_idx, idx.size())); CU(dev_alloc(d_out, 18 * idx.size()));
+        CU(cudaMemcpyAsync(d_idx, idx.data(), 4 * idx.size(), cudaMemcpyHostToDevice, st));
+        e = launch_gather_faces(d_idx, (int)idx.size(), s.pos, s.nrm, d_out, st);
+        std::vector<double> packed(18 * idx.size());
+        if (!e) e = (int)cudaMemcpyAsync(packed.data(), d_out, 8 * packed.size(), cudaMemcpyDeviceToHost, st);
+        if (!e) e = (int)cudaStreamSynchronize(st);
+        cudaFree(d_idx); cudaFree(d_out);
+        if (e) return fail_cuda((cudaError_t)e, "gather light faces");
+        lpos[l].resize(9 * idx.size()); lnrm[l].resize(9 * idx.size());
+        for (size_t j = 0; j < idx.size(); j++) {
+            std::memcpy(&lpos[l][9 * j], &packed[18 * j], 72);
+            std::memcpy(&lnrm[l][9 * j], &packed[18 * j + 9], 72);
+        }
     }
-    c->n_materials = d->n_materials; c->n_textures = d->n_textures; c->n_lights = d->n_lights;
-    CU(dev_alloc(c->d_materials, mats.size())); CU(dev_alloc(c->d_textures, texs.size())); CU(dev_alloc(c->d_tex_bytes, tex_bytes.size()));
-    CU(dev_alloc(c->d_lights, lights.size())); CU(dev_alloc(c->d_light_tris, ltris.size())); CU(dev_alloc(c->d_light_cdf, cdf.size()));
-    CU(cudaMemcpyAsync(c->d_materials, mats.data(), sizeof(DMaterial) * mats.size(), cudaMemcpyHostToDevice, st));
-    if (!texs.empty()) CU(cudaMemcpyAsync(c->d_textures, texs.data(), sizeof(DTexture) * texs.size(), cudaMemcpyHostToDevice, st));
-    if (!tex_bytes.empty()) CU(cudaMemcpyAsync(c->d_tex_bytes, tex_bytes.data(), tex_bytes.size(), cudaMemcpyHostToDevice, st));
-    if (!lights.empty()) CU(cudaMemcpyAsync(c->d_lights, lights.data(), sizeof(DLight) * lights.size(), cudaMemcpyHostToDevice, st));
-    if (!ltris.empty()) CU(cudaMemcpyAsync(c->d_light_tris, ltris.data(), sizeof(LightTri) * ltris.size(), cudaMemcpyHostToDevice, st));
-    if (!cdf.empty()) CU(cudaMemcpyAsync(c->d_light_cdf, cdf.data(), sizeof(float) * cdf.size(), cudaMemcpyHostToDevice, st));
-    CU(cudaStreamSynchronize(st));  // the staging vectors die here
-    c->scene_loaded = true;
+    if (int rc = upload_tables(c, d, lpos, lnrm)) return rc;
+    CU(cudaEventRecord(c->ev1, st));
+    CU(cudaEventSynchronize(c->ev1));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->last_ingest_launches = g.launches;
+    if (ms_out) *ms_out = ms;
+    return MCPT_OK;
+}
+
+MCPT_API int64_t mcpt_scene_face_count(mcpt_ctx* c) {
+    if (!c || !c->scene_loaded) { fail_arg("mcpt_scene_face_count: no scene"); return MCPT_ERR_ARG; }
+    return c->sb.n_faces;
+}
+
+MCPT_API int mcpt_get_scene_arrays(mcpt_ctx* c, double* pos, double* nrm, double* uv, int32_t* mat_id) {
+    if (!c || !c->scene_loaded) return fail_arg("mcpt_get_scene_arrays: no scene");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    const size_t N = (size_t)c->sb.n_faces;
+    if (pos) CU(cudaMemcpy(pos, c->sb.pos, 72 * N, cudaMemcpyDeviceToHost));
+    if (nrm) CU(cudaMemcpy(nrm, c->sb.nrm, 72 * N, cudaMemcpyDeviceToHost));
+    if (uv) CU(cudaMemcpy(uv, c->sb.uv, 48 * N, cudaMemcpyDeviceToHost));
+    if (mat_id) CU(cudaMemcpy(mat_id, c->sb.mat_id, 4 * N, cudaMemcpyDeviceToHost));
     return MCPT_OK;
 }
 
