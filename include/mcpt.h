@@ -157,8 +157,11 @@ MCPT_API int mcpt_upload_scene(mcpt_ctx* ctx, const mcpt_scene_desc* scene);
  * does not (hex floats, inf/nan, > 40 significant digits).  ms_out (may be NULL) = device time incl. the H2D copy. */
 MCPT_API int mcpt_ingest_obj(mcpt_ctx* ctx, const char* obj_text, int64_t n_bytes, const mcpt_scene_desc* tables,
                              const char* const* material_names, float* ms_out);
+/* The same, reading `file` itself: 8 MiB blocks through a pinned ring, each block's H2D copy overlapping the next read. */
+MCPT_API int mcpt_ingest_obj_file(mcpt_ctx* ctx, const char* file, const mcpt_scene_desc* tables,
+                                  const char* const* material_names, float* ms_out);
 /* read_scene (MTPC/sceneManagement.cpp:264-274) with the OBJ on the GPU: <path><name>.mtl and .camera are parsed on the
- * host (a few lines each), the .obj by mcpt_ingest_obj.  Leaves the context as mcpt_upload_scene would. */
+ * host (a few lines each), the .obj by mcpt_ingest_obj_file.  Leaves the context as mcpt_upload_scene would. */
 MCPT_API int mcpt_scene_load_gpu(mcpt_ctx* ctx, const char* path, const char* name, mcpt_camera* camera_out, float* ingest_ms_out);
 /* Parity hooks for the ingest: face count of the resident scene (negative = error) and its flattened arrays
  * (9/9/6 doubles and one int32 per face, HOST buffers; any pointer may be NULL). */

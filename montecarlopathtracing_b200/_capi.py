@@ -56,6 +56,7 @@ SIGNATURES = {
     "mcpt_scene_free": (None, [C.c_void_p]),
     "mcpt_scene_get_material_name": (C.c_char_p, [C.c_void_p, C.c_int32]),
     "mcpt_ingest_obj": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(SceneDesc), C.POINTER(C.c_char_p), C.POINTER(C.c_float)]),
+    "mcpt_ingest_obj_file": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(SceneDesc), C.POINTER(C.c_char_p), C.POINTER(C.c_float)]),
     "mcpt_scene_load_gpu": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(Camera), C.POINTER(C.c_float)]),
     "mcpt_scene_face_count": (C.c_int64, [C.c_void_p]),
     "mcpt_get_scene_arrays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -1,10 +1,13 @@
 // api.cu — the C ABI of include/mcpt.h (device side): context, scene upload, seams 1-3.
 // No CPU fallback: every entry point that computes needs a CUDA device with sm_100a code.
+#include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <type_traits>
 #include <vector>
 #include "lbvh.h"
 #include "render.h"
@@ -33,6 +36,8 @@ struct mcpt_ctx {
     WfHost wfh;                                         // streams/events of the wavefront loop
     void* d_io = nullptr; size_t io_cap = 0;            // scratch: rays in / hits out of mcpt_trace
     char* d_text = nullptr; size_t text_cap = 0;        // scratch: OBJ text of mcpt_ingest_obj
+    DevArena ingest_text, ingest_stmt;                  // scratch: ingest temporaries
+    char* h_pin[2] = {nullptr, nullptr}; cudaEvent_t pin_ev[2] = {nullptr, nullptr};   // pinned ring of mcpt_ingest_obj_file
     int last_ingest_launches = 0;
     float last_build_ms = 0.f;
     bool scene_loaded = false;
@@ -61,10 +66,7 @@ template <class T> cudaError_t grow(T*& p, size_t& cap, size_t bytes) {
 }
 void free_scene(mcpt_ctx* c) {
     SceneBuffers& s = c->sb;
-    cudaFree(s.pos); cudaFree(s.nrm); cudaFree(s.uv); cudaFree(s.mat_id); cudaFree(s.codes_obj); cudaFree(s.codes_sorted);
-    cudaFree(s.iota); cudaFree(s.leaf_face); cudaFree(s.leaf_parent); cudaFree(s.flags); cudaFree(s.nodes); cudaFree(s.tri);
-    cudaFree(s.shade); cudaFree(s.root_box); cudaFree(s.cub_temp); cudaFree(s.qnodes); cudaFree(s.qgrid); cudaFree(s.nodes2); cudaFree(s.cl_lo[0]); cudaFree(s.cl_lo[1]); cudaFree(s.cl_hi[0]);
-    cudaFree(s.cl_hi[1]); cudaFree(s.ploc_nn); cudaFree(s.ploc_flag); cudaFree(s.ploc_scan); cudaFree(s.ploc_temp); cudaFree(s.ploc_state);
+    cudaFree(s.arena);
     s = SceneBuffers();
     cudaFree(c->d_materials); cudaFree(c->d_textures); cudaFree(c->d_tex_bytes); cudaFree(c->d_lights);
     cudaFree(c->d_light_tris); cudaFree(c->d_light_cdf);
@@ -107,18 +109,32 @@ int alloc_scene(mcpt_ctx* c, int n) {
     SceneBuffers& s = c->sb;
     s.n_faces = n;
     const size_t N = (size_t)n;
-    CU(dev_alloc(s.pos, 9 * N)); CU(dev_alloc(s.nrm, 9 * N)); CU(dev_alloc(s.uv, 6 * N)); CU(dev_alloc(s.mat_id, N));
-    CU(dev_alloc(s.codes_obj, N)); CU(dev_alloc(s.codes_sorted, N)); CU(dev_alloc(s.iota, N)); CU(dev_alloc(s.leaf_face, N));
-    CU(dev_alloc(s.leaf_parent, N)); CU(dev_alloc(s.flags, N)); CU(dev_alloc(s.nodes, N)); CU(dev_alloc(s.tri, N));
-    CU(dev_alloc(s.shade, N)); CU(dev_alloc(s.root_box, 6)); CU(dev_alloc(s.qnodes, N)); CU(dev_alloc(s.qgrid, 1));
-    CU(dev_alloc(s.nodes2, N)); CU(dev_alloc(s.cl_lo[0], N)); CU(dev_alloc(s.cl_lo[1], N)); CU(dev_alloc(s.cl_hi[0], N)); CU(dev_alloc(s.cl_hi[1], N));
-    CU(dev_alloc(s.ploc_nn, N)); CU(dev_alloc(s.ploc_flag, N)); CU(dev_alloc(s.ploc_scan, N));
     s.ploc_temp_bytes = ploc_scan_temp_bytes(n);
-    CU(cudaMalloc(&s.ploc_temp, s.ploc_temp_bytes ? s.ploc_temp_bytes : 1));
-    CU(cudaMalloc(&s.ploc_state, 64));
-    { const char* v = getenv("MCPT_BVH"); s.use_ploc = !(v && std::strcmp(v, "lbvh") == 0); }
     s.cub_temp_bytes = lbvh_sort_temp_bytes(n);
-    CU(cudaMalloc(&s.cub_temp, s.cub_temp_bytes ? s.cub_temp_bytes : 1));
+    { const char* v = getenv("MCPT_BVH"); s.use_ploc = !(v && std::strcmp(v, "lbvh") == 0); }
+    // one allocation, carved (a scene of n faces needs ~30 arrays; 30 cudaMalloc/cudaFree pairs cost more than a small build)
+    char* base = nullptr;
+    size_t used = 0;
+    auto carve = [&](auto*& p, size_t count) {
+        using T = std::remove_reference_t<decltype(*p)>;
+        if (base) p = (T*)(base + used);
+        used += (sizeof(T) * (count ? count : 1) + 255) & ~(size_t)255;
+    };
+    auto carve_bytes = [&](void*& p, size_t bytes) {
+        if (base) p = base + used;
+        used += ((bytes ? bytes : 1) + 255) & ~(size_t)255;
+    };
+    for (int pass = 0; pass < 2; pass++) {
+        used = 0;
+        carve(s.pos, 9 * N); carve(s.nrm, 9 * N); carve(s.uv, 6 * N); carve(s.mat_id, N);
+        carve(s.codes_obj, N); carve(s.codes_sorted, N); carve(s.iota, N); carve(s.leaf_face, N);
+        carve(s.leaf_parent, N); carve(s.flags, N); carve(s.nodes, N); carve(s.tri, N);
+        carve(s.shade, N); carve(s.root_box, 6); carve(s.qnodes, N); carve(s.qgrid, 1);
+        carve(s.nodes2, N); carve(s.cl_lo[0], N); carve(s.cl_lo[1], N); carve(s.cl_hi[0], N); carve(s.cl_hi[1], N);
+        carve(s.ploc_nn, N); carve(s.ploc_flag, N); carve(s.ploc_scan, N);
+        carve_bytes(s.ploc_temp, s.ploc_temp_bytes); carve_bytes(s.ploc_state, 64); carve_bytes(s.cub_temp, s.cub_temp_bytes);
+        if (pass == 0) { CU(cudaMalloc((void**)&base, used)); s.arena = base; }
+    }
     return MCPT_OK;
 }
 
@@ -190,6 +206,89 @@ int upload_tables(mcpt_ctx* c, const mcpt_scene_desc* d, const std::vector<std::
     c->scene_loaded = true;
     return MCPT_OK;
 }
+
+// mcpt_ingest_obj after the text is on its way to c->d_text (ev0 recorded): parse, flatten, tables
+int ingest_resident(mcpt_ctx* c, int64_t n_bytes, const mcpt_scene_desc* d, const char* const* names, float* ms_out) {
+    cudaStream_t st = c->stream;
+    ObjIngest g;
+    g.d_text = c->d_text; g.n_bytes = (unsigned)n_bytes;
+    g.arena_text = &c->ingest_text; g.arena_stmt = &c->ingest_stmt;
+    const bool timing = getenv("MCPT_INGEST_TIMING") != nullptr;   // host wall clock per phase, to stderr
+    auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[ingest] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
+    int e = obj_ingest_parse(g, st);
+    lap("H2D wait + count/scan/parse");
+    if (e) return fail_cuda((cudaError_t)e, "obj_ingest_parse");
+    auto obj_error = [&](unsigned long long w) {
+        static const char* what[] = {"", "only triangles are supported (as in the reference)", "face uses unknown material",
+                                     "face index out of range", "number not readable the way atof reads it (hex / inf / nan / > 40 digits)"};
+        const unsigned code = (unsigned)(w & 0xFF);
+        std::string m = std::string("obj: ") + what[code < 5 ? code : 0] + " (line at byte offset " + std::to_string(w >> 8) + ")";
+        mcpt_set_error(m.c_str());
+        return (int)MCPT_ERR_IO;
+    };
+    if (g.n_f == 0) {                                   // errors wait for stage 2: an unknown material on an earlier line comes first
+        if (g.h_status[0] != ~0ull) return obj_error(g.h_status[0]);
+        mcpt_set_error("obj: no faces");
+        return MCPT_ERR_IO;
+    }
+    std::vector<std::string> um_names;
+    e = obj_ingest_names(g, um_names, st);
+    if (e) return fail_cuda((cudaError_t)e, "obj_ingest_names");
+    std::vector<int> um_mat(um_names.size(), -1);
+    for (size_t i = 0; i < um_names.size(); i++)
+        for (int m = 0; m < d->n_materials; m++)
+            if (names[m] && um_names[i] == names[m]) um_mat[i] = m;   // a repeated newmtl name keeps one entry (scene_loader.cpp)
+    lap("usemtl names");
+    if (int rc = alloc_scene(c, (int)g.n_f)) return rc;
+    lap("alloc_scene");
+    SceneBuffers& s = c->sb;
+    e = obj_ingest_flatten(g, um_mat.data(), s.pos, s.nrm, s.uv, s.mat_id, st);
+    if (e) return fail_cuda((cudaError_t)e, "obj_ingest_flatten");
+    if (g.h_status[0] != ~0ull) { free_scene(c); return obj_error(g.h_status[0]); }
+    lap("flatten");
+    // light faces: material ids back to the host (4 B per face), index lists per light, one gather per light
+    const int n = (int)g.n_f;
+    std::vector<int> mat((size_t)n);
+    CU(cudaMemcpyAsync(mat.data(), s.mat_id, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    std::vector<std::vector<double>> lpos(d->n_lights), lnrm(d->n_lights);
+    for (int l = 0; l < d->n_lights; l++) {
+        std::vector<int> idx;
+        for (int i = 0; i < n; i++) if (mat[i] == d->lights[l].mat_id) idx.push_back(i);
+        if (idx.empty()) continue;
+        int* d_idx = nullptr; double* d_out = nullptr;
+        CU(dev_alloc(d_idx, idx.size())); CU(dev_alloc(d_out, 18 * idx.size()));
+        CU(cudaMemcpyAsync(d_idx, idx.data(), 4 * idx.size(), cudaMemcpyHostToDevice, st));
+        e = launch_gather_faces(d_idx, (int)idx.size(), s.pos, s.nrm, d_out, st);
+        std::vector<double> packed(18 * idx.size());
+        if (!e) e = (int)cudaMemcpyAsync(packed.data(), d_out, 8 * packed.size(), cudaMemcpyDeviceToHost, st);
+        if (!e) e = (int)cudaStreamSynchronize(st);
+        cudaFree(d_idx); cudaFree(d_out);
+        if (e) return fail_cuda((cudaError_t)e, "gather light faces");
+        lpos[l].resize(9 * idx.size()); lnrm[l].resize(9 * idx.size());
+        for (size_t j = 0; j < idx.size(); j++) {
+            std::memcpy(&lpos[l][9 * j], &packed[18 * j], 72);
+            std::memcpy(&lnrm[l][9 * j], &packed[18 * j + 9], 72);
+        }
+    }
+    lap("light faces");
+    if (int rc = upload_tables(c, d, lpos, lnrm)) return rc;
+    lap("tables");
+    CU(cudaEventRecord(c->ev1, st));
+    CU(cudaEventSynchronize(c->ev1));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->last_ingest_launches = g.launches;
+    if (ms_out) *ms_out = ms;
+    return MCPT_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -222,7 +321,8 @@ MCPT_API void mcpt_destroy(mcpt_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     free_scene(c);
-    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); cudaFree(c->d_png); cudaFree(c->d_text); c->wfh.destroy();
+    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); cudaFree(c->d_png); cudaFree(c->d_text); c->ingest_text.release(); c->ingest_stmt.release(); c->wfh.destroy();
+    for (int k = 0; k < 2; k++) { if (c->h_pin[k]) cudaFreeHost(c->h_pin[k]); if (c->pin_ev[k]) cudaEventDestroy(c->pin_ev[k]); }
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->own_stream);
     delete c;
@@ -279,69 +379,41 @@ MCPT_API int mcpt_ingest_obj(mcpt_ctx* c, const char* text, int64_t n_bytes, con
     CU(cudaEventRecord(c->ev0, st));
     CU(grow(c->d_text, c->text_cap, (size_t)n_bytes));
     CU(cudaMemcpyAsync(c->d_text, text, (size_t)n_bytes, cudaMemcpyHostToDevice, st));
-    ObjIngest g;
-    g.d_text = c->d_text; g.n_bytes = (unsigned)n_bytes;
-    struct Guard { ObjIngest& g; ~Guard() { obj_ingest_free(g); } } guard{g};
-    int e = obj_ingest_parse(g, st);
-    if (e) return fail_cuda((cudaError_t)e, "obj_ingest_parse");
-    auto obj_error = [&](unsigned long long w) {
-        static const char* what[] = {"", "only triangles are supported (as in the reference)", "face uses unknown material",
-                                     "face index out of range", "number not readable the way atof reads it (hex / inf / nan / > 40 digits)"};
-        const unsigned code = (unsigned)(w & 0xFF);
-        std::string m = std::string("obj: ") + what[code < 5 ? code : 0] + " (line at byte offset " + std::to_string(w >> 8) + ")";
-        mcpt_set_error(m.c_str());
-        return (int)MCPT_ERR_IO;
-    };
-    if (g.n_f == 0) {                                   // errors wait for stage 2: an unknown material on an earlier line comes first
-        if (g.h_status[0] != ~0ull) return obj_error(g.h_status[0]);
-        mcpt_set_error("obj: no faces");
-        return MCPT_ERR_IO;
+    return ingest_resident(c, n_bytes, d, names, ms_out);
+}
+
+/* The same from a file: read in 8 MiB blocks into a pinned ring, each block's H2D copy overlapping the next read. */
+MCPT_API int mcpt_ingest_obj_file(mcpt_ctx* c, const char* file, const mcpt_scene_desc* d, const char* const* names, float* ms_out) {
+    if (!c || !file || !d || !names) return fail_arg("mcpt_ingest_obj_file: null argument");
+    if (int rc = check_tables(d, "mcpt_ingest_obj_file")) return rc;
+    FILE* f = std::fopen(file, "rb");
+    if (!f) { mcpt_set_error((std::string("cannot open ") + file).c_str()); return MCPT_ERR_IO; }
+    struct Closer { FILE* f; ~Closer() { std::fclose(f); } } closer{f};
+    std::fseek(f, 0, SEEK_END);
+    const long long n_bytes = std::ftell(f);
+    std::fseek(f, 0, SEEK_SET);
+    if (n_bytes <= 0) { mcpt_set_error((std::string(file) + ": no faces").c_str()); return MCPT_ERR_IO; }
+    if (n_bytes >= 0xFFFFFF00ll) return fail_arg("mcpt_ingest_obj_file: file must be < 4 GiB");
+    CU(cudaSetDevice(c->device));
+    free_scene(c);
+    cudaStream_t st = c->stream;
+    const size_t BLOCK = 8u << 20;
+    for (int k = 0; k < 2; k++) {
+        if (!c->h_pin[k]) CU(cudaHostAlloc((void**)&c->h_pin[k], BLOCK, cudaHostAllocDefault));
+        if (!c->pin_ev[k]) CU(cudaEventCreateWithFlags(&c->pin_ev[k], cudaEventDisableTiming));
     }
-    std::vector<std::string> um_names;
-    e = obj_ingest_names(g, um_names, st);
-    if (e) return fail_cuda((cudaError_t)e, "obj_ingest_names");
-    std::vector<int> um_mat(um_names.size(), -1);
-    for (size_t i = 0; i < um_names.size(); i++)
-        for (int m = 0; m < d->n_materials; m++)
-            if (names[m] && um_names[i] == names[m]) um_mat[i] = m;   // a repeated newmtl name keeps one entry (scene_loader.cpp)
-    if (int rc = alloc_scene(c, (int)g.n_f)) return rc;
-    SceneBuffers& s = c->sb;
-    e = obj_ingest_flatten(g, um_mat.data(), s.pos, s.nrm, s.uv, s.mat_id, st);
-    if (e) return fail_cuda((cudaError_t)e, "obj_ingest_flatten");
-    if (g.h_status[0] != ~0ull) { free_scene(c); return obj_error(g.h_status[0]); }
-    // light faces: material ids back to the host (4 B per face), index lists per light, one gather per light
-    const int n = (int)g.n_f;
-    std::vector<int> mat((size_t)n);
-    CU(cudaMemcpyAsync(mat.data(), s.mat_id, 4 * (size_t)n, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-    std::vector<std::vector<double>> lpos(d->n_lights), lnrm(d->n_lights);
-    for (int l = 0; l < d->n_lights; l++) {
-        std::vector<int> idx;
-        for (int i = 0; i < n; i++) if (mat[i] == d->lights[l].mat_id) idx.push_back(i);
-        if (idx.empty()) continue;
-        int* d_idx = nullptr; double* d_out = nullptr;
-        CU(dev_alloc(d_idx, idx.size())); CU(dev_alloc(d_out, 18 * idx.size()));
-        CU(cudaMemcpyAsync(d_idx, idx.data(), 4 * idx.size(), cudaMemcpyHostToDevice, st));
-        e = launch_gather_faces(d_idx, (int)idx.size(), s.pos, s.nrm, d_out, st);
-        std::vector<double> packed(18 * idx.size());
-        if (!e) e = (int)cudaMemcpyAsync(packed.data(), d_out, 8 * packed.size(), cudaMemcpyDeviceToHost, st);
-        if (!e) e = (int)cudaStreamSynchronize(st);
-        cudaFree(d_idx); cudaFree(d_out);
-        if (e) return fail_cuda((cudaError_t)e, "gather light faces");
-        lpos[l].resize(9 * idx.size()); lnrm[l].resize(9 * idx.size());
-        for (size_t j = 0; j < idx.size(); j++) {
-            std::memcpy(&lpos[l][9 * j], &packed[18 * j], 72);
-            std::memcpy(&lnrm[l][9 * j], &packed[18 * j + 9], 72);
-        }
+    CU(cudaEventRecord(c->ev0, st));
+    CU(grow(c->d_text, c->text_cap, (size_t)n_bytes));
+    size_t off = 0;
+    for (int k = 0; off < (size_t)n_bytes; k ^= 1) {
+        const size_t len = std::min(BLOCK, (size_t)n_bytes - off);
+        CU(cudaEventSynchronize(c->pin_ev[k]));           // the copy that last used this buffer (a fresh event is complete)
+        if (std::fread(c->h_pin[k], 1, len, f) != len) { mcpt_set_error((std::string("cannot read ") + file).c_str()); return MCPT_ERR_IO; }
+        CU(cudaMemcpyAsync(c->d_text + off, c->h_pin[k], len, cudaMemcpyHostToDevice, st));
+        CU(cudaEventRecord(c->pin_ev[k], st));
+        off += len;
     }
-    if (int rc = upload_tables(c, d, lpos, lnrm)) return rc;
-    CU(cudaEventRecord(c->ev1, st));
-    CU(cudaEventSynchronize(c->ev1));
-    float ms = 0.f;
-    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
-    c->last_ingest_launches = g.launches;
-    if (ms_out) *ms_out = ms;
-    return MCPT_OK;
+    return ingest_resident(c, n_bytes, d, names, ms_out);
 }
 
 MCPT_API int64_t mcpt_scene_face_count(mcpt_ctx* c) {

@@ -29,6 +29,7 @@ struct SceneBuffers {
     int* ploc_nn = nullptr; unsigned long long* ploc_flag = nullptr; unsigned long long* ploc_scan = nullptr;
     void* ploc_temp = nullptr; size_t ploc_temp_bytes = 0; void* ploc_state = nullptr;
     int root = 0;                      // root of the traversal tree (0: radix tree, n-2: PLOC tree)
+    void* arena = nullptr;             // every pointer above is carved from this one allocation (api.cu alloc_scene)
     bool built = false;
 };
 

@@ -213,8 +213,15 @@ __global__ void gather_faces_kernel(const int* __restrict__ idx, int m, const do
 }
 
 namespace {
-template <class T> cudaError_t alloc(T*& p, size_t count) { return cudaMalloc((void**)&p, sizeof(T) * (count ? count : 1)); }
 #define OBJ_CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return (int)e_; } while (0)
+struct Carver {
+    char* base; size_t used = 0;
+    explicit Carver(char* b) : base(b) {}
+    template <class T> void take(T*& p, size_t count) {
+        if (base) p = (T*)(base + used);
+        used += (sizeof(T) * (count ? count : 1) + 255) & ~(size_t)255;
+    }
+};
 }  // namespace
 
 int obj_ingest_parse(ObjIngest& g, cudaStream_t st) {
@@ -222,16 +229,18 @@ int obj_ingest_parse(ObjIngest& g, cudaStream_t st) {
     g.n_chunks = (n + OBJ_CHUNK - 1) / OBJ_CHUNK;
     const unsigned nc1 = g.n_chunks + 1;
     ObjCounts* counts = nullptr;
-    OBJ_CU(alloc(counts, nc1));
-    g.counts = counts;
-    OBJ_CU(alloc(g.defer, g.n_chunks));
-    OBJ_CU(alloc(g.status, 2));
+    ObjCounts zero = {0, 0, 0, 0, 0, 0, 0, 0};
+    OBJ_CU(cub::DeviceScan::ExclusiveScan(nullptr, g.scan_temp_bytes, counts, counts, ObjCountsSum(), zero, (int)nc1, st));
+    char* scan_temp = nullptr;
+    for (int pass = 0; pass < 2; pass++) {
+        Carver c(pass ? g.arena_text->base : nullptr);
+        c.take(counts, nc1); c.take(g.defer, g.n_chunks); c.take(g.status, 2); c.take(scan_temp, g.scan_temp_bytes);
+        if (pass == 0) OBJ_CU(g.arena_text->reserve(c.used));
+    }
+    g.counts = counts; g.scan_temp = scan_temp;
     OBJ_CU(cudaMemsetAsync(g.defer, 0, g.n_chunks ? g.n_chunks : 1, st));
     const unsigned long long init[2] = {~0ull, 0ull};
     OBJ_CU(cudaMemcpyAsync(g.status, init, 16, cudaMemcpyHostToDevice, st));
-    ObjCounts zero = {0, 0, 0, 0, 0, 0, 0, 0};
-    OBJ_CU(cub::DeviceScan::ExclusiveScan(nullptr, g.scan_temp_bytes, counts, counts, ObjCountsSum(), zero, (int)nc1, st));
-    OBJ_CU(cudaMalloc(&g.scan_temp, g.scan_temp_bytes ? g.scan_temp_bytes : 1));
     const unsigned blocks = (nc1 + 127) / 128;
     obj_count_kernel<<<blocks, 128, 0, st>>>(g.d_text, n, g.n_chunks, counts);
     OBJ_CU(cub::DeviceScan::ExclusiveScan(g.scan_temp, g.scan_temp_bytes, counts, counts, ObjCountsSum(), zero, (int)nc1, st));
@@ -240,9 +249,13 @@ int obj_ingest_parse(ObjIngest& g, cudaStream_t st) {
     OBJ_CU(cudaStreamSynchronize(st));
     g.n_v = total.v; g.n_vn = total.vn; g.n_vt = total.vt; g.n_f = total.f; g.n_um = total.um;
     g.launches += 2;
-    OBJ_CU(alloc(g.v, 3ull * g.n_v)); OBJ_CU(alloc(g.vn, 3ull * g.n_vn)); OBJ_CU(alloc(g.vt, 2ull * g.n_vt));
-    OBJ_CU(alloc(g.fidx, 9ull * g.n_f)); OBJ_CU(alloc(g.f_um, g.n_f)); OBJ_CU(alloc(g.f_off, g.n_f));
-    OBJ_CU(alloc(g.um_off, g.n_um)); OBJ_CU(alloc(g.um_len, g.n_um)); OBJ_CU(alloc(g.um_mat, g.n_um));
+    for (int pass = 0; pass < 2; pass++) {
+        Carver c(pass ? g.arena_stmt->base : nullptr);
+        c.take(g.v, 3ull * g.n_v); c.take(g.vn, 3ull * g.n_vn); c.take(g.vt, 2ull * g.n_vt);
+        c.take(g.fidx, 9ull * g.n_f); c.take(g.f_um, g.n_f); c.take(g.f_off, g.n_f);
+        c.take(g.um_off, g.n_um); c.take(g.um_len, g.n_um); c.take(g.um_mat, g.n_um);
+        if (pass == 0) OBJ_CU(g.arena_stmt->reserve(c.used));
+    }
     if (g.n_chunks) {
         const unsigned pb = (g.n_chunks + 127) / 128;
         obj_parse_kernel<false><<<pb, 128, 0, st>>>(g.d_text, n, g.n_chunks, counts, g.defer, g.v, g.vn, g.vt, g.fidx, g.f_um, g.f_off, g.um_off, g.um_len, g.status);
@@ -268,7 +281,7 @@ int obj_ingest_names(ObjIngest& g, std::vector<std::string>& names, cudaStream_t
     size_t total = 0;
     for (unsigned i = 0; i < g.n_um; i++) { dst[i] = (unsigned)total; total += len[i]; }
     unsigned* d_dst = nullptr; char* d_out = nullptr;
-    OBJ_CU(alloc(d_dst, g.n_um)); OBJ_CU(alloc(d_out, total));
+    OBJ_CU(cudaMalloc((void**)&d_dst, 4ull * g.n_um)); OBJ_CU(cudaMalloc((void**)&d_out, total ? total : 1));
     OBJ_CU(cudaMemcpyAsync(d_dst, dst.data(), 4ull * g.n_um, cudaMemcpyHostToDevice, st));
     obj_pack_names_kernel<<<(g.n_um + 127) / 128, 128, 0, st>>>(g.d_text, g.n_um, g.um_off, g.um_len, d_dst, d_out);
     g.launches++;
@@ -289,14 +302,6 @@ int obj_ingest_flatten(ObjIngest& g, const int* um_mat, double* d_pos, double* d
     OBJ_CU(cudaMemcpyAsync(g.h_status, g.status, 16, cudaMemcpyDeviceToHost, st));
     OBJ_CU(cudaStreamSynchronize(st));
     return (int)cudaGetLastError();
-}
-
-void obj_ingest_free(ObjIngest& g) {
-    cudaFree(g.counts); cudaFree(g.scan_temp); cudaFree(g.defer); cudaFree(g.v); cudaFree(g.vn); cudaFree(g.vt); cudaFree(g.fidx);
-    cudaFree(g.f_um); cudaFree(g.f_off); cudaFree(g.um_off); cudaFree(g.um_len); cudaFree(g.um_mat); cudaFree(g.status);
-    const char* text = g.d_text; const unsigned n = g.n_bytes;
-    g = ObjIngest();
-    g.d_text = text; g.n_bytes = n;
 }
 
 int launch_gather_faces(const int* d_idx, int m, const double* d_pos, const double* d_nrm, double* d_out, cudaStream_t st) {

@@ -10,12 +10,29 @@ namespace mcpt {
 
 enum ObjErrorCode { OBJ_ERR_NOT_TRIANGLE = 1, OBJ_ERR_UNKNOWN_MATERIAL = 2, OBJ_ERR_INDEX_RANGE = 3, OBJ_ERR_NUMBER = 4 };
 
+// Grow-only device scratch owned by the context: the ingest's temporaries are carved from two of these (one sized from the
+// text length, one from the statement counts), so a second ingest allocates nothing.
+struct DevArena {
+    char* base = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap && base) return cudaSuccess;
+        if (base) cudaFree(base);
+        base = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc((void**)&base, bytes ? bytes : 1);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    void release() { if (base) cudaFree(base); base = nullptr; cap = 0; }
+};
+
 struct ObjIngest {
+    DevArena* arena_text = nullptr;   // counts, scan scratch, defer flags, status
+    DevArena* arena_stmt = nullptr;   // parsed statements
     const char* d_text = nullptr;     // the OBJ file, bytes as on disk (not owned)
     unsigned n_bytes = 0;
     unsigned n_chunks = 0;
     unsigned n_v = 0, n_vn = 0, n_vt = 0, n_f = 0, n_um = 0;   // statement counts (host copies)
-    // device temporaries (owned; obj_ingest_free)
+    // device temporaries (carved from the arenas)
     void* counts = nullptr;           // per-chunk statement counts, then their exclusive scan
     void* scan_temp = nullptr; size_t scan_temp_bytes = 0;
     unsigned char* defer = nullptr;   // per chunk: holds a number that needs the 896-bit conversion
@@ -39,7 +56,6 @@ int obj_ingest_names(ObjIngest& g, std::vector<std::string>& names, cudaStream_t
 // Stage 2: per-face material + gather into the flattened scene arrays (K18).  um_mat: host array of n_um material ids.
 // Synchronises the stream and refreshes h_status.
 int obj_ingest_flatten(ObjIngest& g, const int* um_mat, double* d_pos, double* d_nrm, double* d_uv, int* d_mat_id, cudaStream_t stream);
-void obj_ingest_free(ObjIngest& g);
 // out[18 j .. 18 j + 17] = pos[9 idx[j] ..], nrm[9 idx[j] ..]
 int launch_gather_faces(const int* d_idx, int m, const double* d_pos, const double* d_nrm, double* d_out, cudaStream_t stream);
 

@@ -178,20 +178,11 @@ void HostScene::finalize() {
     desc.materials = materials.data(); desc.textures = textures.data(); desc.lights = lights.data();
 }
 
-// read_scene with the OBJ left to the GPU: tables from .mtl / .camera here, the .obj's bytes for mcpt_ingest_obj.
-// A .camera error is held back until the OBJ has been read, to keep the order in which read_scene meets problems.
-void load_tables(const std::string& path, const std::string& name, HostScene& out, std::vector<char>& obj_text, std::string& camera_error) {
+// read_scene with the OBJ left to the GPU: only the tables from .mtl / .camera are read here.  A .camera error is held
+// back until the OBJ has been read, to keep the order in which read_scene meets problems.
+void load_tables(const std::string& path, const std::string& name, HostScene& out, std::string& camera_error) {
     const std::string base = path + name;
     read_mtl(path, base + ".mtl", out);
-    FILE* f = std::fopen((base + ".obj").c_str(), "rb");
-    if (!f) throw std::runtime_error("cannot open " + base + ".obj");
-    std::fseek(f, 0, SEEK_END);
-    const long size = std::ftell(f);
-    std::fseek(f, 0, SEEK_SET);
-    obj_text.resize(size > 0 ? size_t(size) : 0);
-    const bool ok = obj_text.empty() || std::fread(obj_text.data(), 1, obj_text.size(), f) == obj_text.size();
-    std::fclose(f);
-    if (!ok) throw std::runtime_error("cannot read " + base + ".obj");
     try { read_camera(base + ".camera", out); }
     catch (const std::exception& e) { camera_error = e.what(); out.lights.clear(); }
     out.finalize();
@@ -230,15 +221,14 @@ MCPT_API const char* mcpt_scene_get_material_name(const mcpt_host_scene* s, int3
 MCPT_API int mcpt_scene_load_gpu(mcpt_ctx* ctx, const char* path, const char* name, mcpt_camera* camera_out, float* ingest_ms_out) {
     if (!ctx || !path || !name) { mcpt_set_error("mcpt_scene_load_gpu: null argument"); return MCPT_ERR_ARG; }
     mcpt::HostScene hs;
-    std::vector<char> text;
     std::string camera_error;
-    try { mcpt::load_tables(path, name, hs, text, camera_error); }
+    try { mcpt::load_tables(path, name, hs, camera_error); }
     catch (const std::exception& e) { mcpt_set_error(e.what()); return MCPT_ERR_IO; }
-    if (text.empty()) { mcpt_set_error((std::string(path) + name + ".obj: no faces").c_str()); return MCPT_ERR_IO; }
+    const std::string base = std::string(path) + name;
+    if (hs.materials.empty()) { mcpt_set_error((base + ".mtl: no materials").c_str()); return MCPT_ERR_IO; }
     std::vector<const char*> names;
     for (const auto& n : hs.material_names) names.push_back(n.c_str());
-    if (hs.materials.empty()) { mcpt_set_error((std::string(path) + name + ".mtl: no materials").c_str()); return MCPT_ERR_IO; }
-    const int rc = mcpt_ingest_obj(ctx, text.data(), int64_t(text.size()), &hs.desc, names.data(), ingest_ms_out);
+    const int rc = mcpt_ingest_obj_file(ctx, (base + ".obj").c_str(), &hs.desc, names.data(), ingest_ms_out);
     if (rc) return rc;
     if (!camera_error.empty()) { mcpt_set_error(camera_error.c_str()); return MCPT_ERR_IO; }
     if (camera_out) *camera_out = hs.camera;

@@ -28,7 +28,7 @@ struct HostScene {
 // Throws std::runtime_error with a message on a missing file, unknown material, bad index or
 // missing texture sidecar (the reference checks none of these and crashes later).
 void load_scene(const std::string& path, const std::string& name, HostScene& out);
-void load_tables(const std::string& path, const std::string& name, HostScene& out, std::vector<char>& obj_text, std::string& camera_error);
+void load_tables(const std::string& path, const std::string& name, HostScene& out, std::string& camera_error);
 
 }  // namespace mcpt
 
