@@ -140,6 +140,41 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def neighbour_stages(M, ctx, scene_name, w, h):
+    """The steps either side of the path, outside the timed region, wall clock, median of 5:
+    scene ingest (GPU: .obj file -> flattened device arrays; host: the sequential loader + H2D upload) and the output stage
+    (device: quantise + PNG framing on the GPU, D2H of the finished file; host: D2H of the float image + mcpt_write_png)."""
+    import tempfile
+    import numpy as np
+    import torch
+    out = {}
+    med = lambda f, n=5: float(np.median([f() for _ in range(n)]))
+
+    def wall(fn):
+        def run():
+            torch.cuda.synchronize(); t0 = time.perf_counter(); fn(); torch.cuda.synchronize()
+            return (time.perf_counter() - t0) * 1e3
+        return run
+    tmp = tempfile.mkdtemp()
+    if not scene_name.startswith("synthetic"):
+        scenes = os.path.join(ROOT, "scenes") + "/"
+        keep = []
+        def host():
+            s = M.HostScene(scenes, scene_name); ctx.upload_scene(s); keep.append(s)
+        out["ingest"] = {"obj_bytes": os.path.getsize(scenes + scene_name + ".obj"),
+                         "gpu_ms": med(wall(lambda: ctx.load_scene_gpu(scenes, scene_name))), "host_loader_plus_upload_ms": med(wall(host), 3)}
+    img = torch.rand(h * w * 3, device="cuda", dtype=torch.float32)
+    host_img = torch.empty(h * w * 3, dtype=torch.float32).pin_memory()
+    def dev_png():
+        ctx.encode_png(img.data_ptr(), w, h).tofile(os.path.join(tmp, "dev.png"))
+    def host_png():
+        host_img.copy_(img); M.write_png(os.path.join(tmp, "host.png"), host_img.numpy().reshape(h, w, 3))
+    out["output_stage"] = {"png_bytes": int(M.png_size(w, h)), "device_ms": med(wall(dev_png)), "host_ms": med(wall(host_png), 3)}
+    same = open(os.path.join(tmp, "dev.png"), "rb").read() == open(os.path.join(tmp, "host.png"), "rb").read()
+    out["output_stage"]["byte_identical"] = bool(same)
+    return out
+
+
 def run_ours(args):
     import ctypes
     import numpy as np
@@ -298,6 +333,8 @@ def run_ours(args):
                                  "wf_trace launches, so the per-launch average shares the GPU; achieved_over_integrator divides by "
                                  "the wall time of the whole shade+trace loop instead."},
         }
+        if world == 1:
+            line["stages"] = neighbour_stages(M, ctx, scene_name, w, h)
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_reference_sample(scene_name)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
