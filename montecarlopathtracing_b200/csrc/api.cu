@@ -394,14 +394,24 @@ MCPT_API int mcpt_ingest_obj_file(mcpt_ctx* c, const char* file, const mcpt_scen
     std::fseek(f, 0, SEEK_SET);
     if (n_bytes <= 0) { mcpt_set_error((std::string(file) + ": no faces").c_str()); return MCPT_ERR_IO; }
     if (n_bytes >= 0xFFFFFF00ll) return fail_arg("mcpt_ingest_obj_file: file must be < 4 GiB");
+    const bool timing = getenv("MCPT_INGEST_TIMING") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[ingest] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
     CU(cudaSetDevice(c->device));
     free_scene(c);
+    lap("free_scene");
     cudaStream_t st = c->stream;
     const size_t BLOCK = 8u << 20;
     for (int k = 0; k < 2; k++) {
         if (!c->h_pin[k]) CU(cudaHostAlloc((void**)&c->h_pin[k], BLOCK, cudaHostAllocDefault));
         if (!c->pin_ev[k]) CU(cudaEventCreateWithFlags(&c->pin_ev[k], cudaEventDisableTiming));
     }
+    lap("pinned ring");
     CU(cudaEventRecord(c->ev0, st));
     CU(grow(c->d_text, c->text_cap, (size_t)n_bytes));
     size_t off = 0;
@@ -413,6 +423,7 @@ MCPT_API int mcpt_ingest_obj_file(mcpt_ctx* c, const char* file, const mcpt_scen
         CU(cudaEventRecord(c->pin_ev[k], st));
         off += len;
     }
+    lap("file read + H2D enqueue");
     return ingest_resident(c, n_bytes, d, names, ms_out);
 }
 
