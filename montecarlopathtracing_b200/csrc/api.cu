@@ -377,7 +377,7 @@ MCPT_API int mcpt_ingest_obj(mcpt_ctx* c, const char* text, int64_t n_bytes, con
     free_scene(c);
     cudaStream_t st = c->stream;
     CU(cudaEventRecord(c->ev0, st));
-    CU(grow(c->d_text, c->text_cap, (size_t)n_bytes));
+    CU(grow(c->d_text, c->text_cap, (size_t)n_bytes + 16));   // the staging loop reads whole words
     CU(cudaMemcpyAsync(c->d_text, text, (size_t)n_bytes, cudaMemcpyHostToDevice, st));
     return ingest_resident(c, n_bytes, d, names, ms_out);
 }
@@ -413,7 +413,7 @@ MCPT_API int mcpt_ingest_obj_file(mcpt_ctx* c, const char* file, const mcpt_scen
     }
     lap("pinned ring");
     CU(cudaEventRecord(c->ev0, st));
-    CU(grow(c->d_text, c->text_cap, (size_t)n_bytes));
+    CU(grow(c->d_text, c->text_cap, (size_t)n_bytes + 16));   // the staging loop reads whole words
     size_t off = 0;
     for (int k = 0; off < (size_t)n_bytes; k ^= 1) {
         const size_t len = std::min(BLOCK, (size_t)n_bytes - off);

@@ -37,8 +37,52 @@ struct ObjCountsSum {
 
 __device__ __forceinline__ bool blank(char c) { return c == ' ' || c == '\t' || c == '\r'; }
 
+// The block's stretch of text staged in shared memory.  A thread walks its own 128-byte chunk byte by byte, so a warp's
+// 32 loads are 128 bytes apart: from global memory that is 32 L1 wavefronts per load instruction (what bounded the first
+// version of these kernels).  In shared memory one pad word per 128 bytes puts the 32 chunks on 32 different banks.
+// Bytes outside the staged window (a line longer than the look-ahead) fall back to global memory.
+#define OBJ_BLOCK 128u
+#define OBJ_SPAN (OBJ_BLOCK * OBJ_CHUNK)   // 16 KiB of text per block
+#define OBJ_BACK 16u                       // look-behind (one byte is needed; 16 keeps the window aligned)
+#define OBJ_LOOK 2048u                     // look-ahead for lines that run past the block's end
+#define OBJ_SMEM_WORDS (((OBJ_BACK + OBJ_SPAN + OBJ_LOOK) / 4u) * 33u / 32u + 2u)
+
+struct TextView {
+    const char* g; const unsigned char* s; unsigned lo, len;
+    __device__ __forceinline__ char operator[](unsigned i) const {
+        const unsigned x = i - lo;
+        return x < len ? (char)s[x + ((x >> 7) << 2)] : g[i];
+    }
+};
+struct TextIt {                            // the iterator obj_number.cuh parses through
+    const TextView* v; unsigned i;
+    __device__ __forceinline__ char operator*() const { return (*v)[i]; }
+    __device__ __forceinline__ char operator[](int k) const { return (*v)[i + k]; }
+    __device__ __forceinline__ TextIt& operator++() { i++; return *this; }
+    __device__ __forceinline__ TextIt operator++(int) { TextIt t = *this; i++; return t; }
+    __device__ __forceinline__ TextIt operator+(int k) const { return TextIt{v, i + k}; }
+    __device__ __forceinline__ int operator-(const TextIt& o) const { return (int)(i - o.i); }
+    __device__ __forceinline__ bool operator<(const TextIt& o) const { return i < o.i; }
+    __device__ __forceinline__ bool operator==(const TextIt& o) const { return i == o.i; }
+};
+
+// Stage [block_begin - OBJ_BACK, block_begin + OBJ_SPAN + OBJ_LOOK) ∩ [0, n); the text buffer has 16 spare bytes.
+__device__ __forceinline__ TextView stage_text(const char* __restrict__ t, unsigned n, unsigned* smem) {
+    const unsigned b0 = blockIdx.x * OBJ_SPAN;
+    TextView v;
+    v.g = t; v.s = (const unsigned char*)smem;
+    v.lo = b0 >= OBJ_BACK ? b0 - OBJ_BACK : 0u;
+    const unsigned long long want = (unsigned long long)b0 + OBJ_SPAN + OBJ_LOOK;
+    const unsigned hi = want < n ? (unsigned)want : n;
+    v.len = hi > v.lo ? hi - v.lo : 0u;
+    const unsigned* src = (const unsigned*)(t + v.lo);
+    for (unsigned w = threadIdx.x; w < (v.len + 3u) / 4u; w += blockDim.x) smem[w + (w >> 5)] = __ldg(src + w);
+    __syncthreads();
+    return v;
+}
+
 // first line start inside [c0, c1), or 0xFFFFFFFF
-__device__ __forceinline__ unsigned first_line_start(const char* __restrict__ t, unsigned c0, unsigned c1, unsigned n) {
+__device__ __forceinline__ unsigned first_line_start(const TextView& t, unsigned c0, unsigned c1, unsigned n) {
     if (c0 == 0) return 0;
     const unsigned lim = c1 < n ? c1 : n;
     unsigned j = c0 - 1;
@@ -47,28 +91,42 @@ __device__ __forceinline__ unsigned first_line_start(const char* __restrict__ t,
 }
 
 // The line [s, le): kind from its first token; `rest` = first byte after that token (for usemtl: start of the name)
-__device__ __forceinline__ int classify_line(const char* __restrict__ t, unsigned s, unsigned n, unsigned& le, unsigned& rest) {
-    unsigned e = s;
-    while (e < n && t[e] != '\n') e++;
+__device__ __forceinline__ int classify_line(const TextView& t, unsigned s, unsigned n, unsigned& le, unsigned& rest) {
+    unsigned p = s;
+    while (p < n && blank(t[p])) p++;                   // '\n' is not a blank: stops at the line end
+    unsigned q = p;
+    char c0 = 0, c1 = 0;
+    bool usemtl = true;
+    while (q < n) {
+        const char c = t[q];
+        if (c == '\n' || blank(c)) break;
+        const unsigned k = q - p;
+        if (k == 0) c0 = c; else if (k == 1) c1 = c;
+        if (k < 6) usemtl = usemtl && c == "usemtl"[k];
+        q++;
+    }
+    rest = q;
+    unsigned e = q;
+    bool more = false;                                  // a second token on the line
+    unsigned r = q;
+    while (e < n) {
+        const char c = t[e];
+        if (c == '\n') break;
+        if (!more && !blank(c)) { more = true; r = e; }
+        e++;
+    }
     le = e;
     if (e - s < 2) return L_NONE;                       // scene_loader.cpp: lines shorter than 2 bytes are skipped
-    unsigned p = s;
-    while (p < e && blank(t[p])) p++;
-    unsigned q = p;
-    while (q < e && !blank(t[q])) q++;
-    rest = q;
     const unsigned len = q - p;
-    if (len == 1) return t[p] == 'v' ? L_V : (t[p] == 'f' ? L_F : L_NONE);
-    if (len == 2 && t[p] == 'v') return t[p + 1] == 'n' ? L_VN : (t[p + 1] == 't' ? L_VT : L_NONE);
-    if (len == 6 && t[p] == 'u' && t[p + 1] == 's' && t[p + 2] == 'e' && t[p + 3] == 'm' && t[p + 4] == 't' && t[p + 5] == 'l') {
-        unsigned r = q;
-        while (r < e && blank(t[r])) r++;
-        if (r < e) { rest = r; return L_UM; }           // a bare "usemtl" changes nothing
-    }
+    if (len == 1) return c0 == 'v' ? L_V : (c0 == 'f' ? L_F : L_NONE);
+    if (len == 2 && c0 == 'v') return c1 == 'n' ? L_VN : (c1 == 't' ? L_VT : L_NONE);
+    if (len == 6 && usemtl && more) { rest = r; return L_UM; }   // a bare "usemtl" changes nothing
     return L_NONE;
 }
 
-__global__ void __launch_bounds__(128) obj_count_kernel(const char* __restrict__ t, unsigned n, unsigned n_chunks, ObjCounts* __restrict__ counts) {
+__global__ void __launch_bounds__(128) obj_count_kernel(const char* __restrict__ text, unsigned n, unsigned n_chunks, ObjCounts* __restrict__ counts) {
+    __shared__ unsigned smem[OBJ_SMEM_WORDS];
+    const TextView t = stage_text(text, n, smem);
     const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c > n_chunks) return;
     ObjCounts k = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -85,7 +143,7 @@ __global__ void __launch_bounds__(128) obj_count_kernel(const char* __restrict__
     counts[c] = k;
 }
 
-__device__ __forceinline__ bool next_tok(const char* __restrict__ t, unsigned& p, unsigned e, unsigned& b, unsigned& en) {
+__device__ __forceinline__ bool next_tok(const TextView& t, unsigned& p, unsigned e, unsigned& b, unsigned& en) {
     while (p < e && blank(t[p])) p++;
     if (p >= e) return false;
     b = p;
@@ -98,27 +156,28 @@ __device__ __forceinline__ void report(unsigned long long* status, unsigned line
 }
 
 // "a/b/c" -> 0-based (v, vn, vt); missing parts repeat the first (scene_loader.cpp parse_corner)
-__device__ __forceinline__ void parse_corner(const char* b, const char* en, long long idx[3]) {
-    idx[0] = objnum::parse_long(b, en) - 1;
+__device__ __forceinline__ void parse_corner(const TextView& t, unsigned b, unsigned en, long long idx[3]) {
+    const TextIt end{&t, en};
+    idx[0] = objnum::parse_long(TextIt{&t, b}, end) - 1;
     idx[1] = idx[2] = idx[0];
-    const char* s1 = b;
-    while (s1 < en && *s1 != '/') s1++;
+    unsigned s1 = b;
+    while (s1 < en && t[s1] != '/') s1++;
     if (s1 == en) return;
-    idx[1] = objnum::parse_long(s1 + 1, en) - 1;
-    const char* s2 = s1 + 1;
-    while (s2 < en && *s2 != '/') s2++;
+    idx[1] = objnum::parse_long(TextIt{&t, s1 + 1}, end) - 1;
+    unsigned s2 = s1 + 1;
+    while (s2 < en && t[s2] != '/') s2++;
     if (s2 == en) return;
-    idx[2] = objnum::parse_long(s2 + 1, en) - 1;
+    idx[2] = objnum::parse_long(TextIt{&t, s2 + 1}, end) - 1;
 }
 
 template <bool BIG>
-__device__ __forceinline__ void parse_numbers(const char* __restrict__ t, unsigned p, unsigned le, unsigned line, int count, double* __restrict__ out,
+__device__ __forceinline__ void parse_numbers(const TextView& t, unsigned p, unsigned le, unsigned line, int count, double* __restrict__ out,
                                               bool& deferred, unsigned long long* status) {
     for (int k = 0; k < count; k++) {
         unsigned b, en;
         double val = 0.0;                               // a missing token reads as 0 (Tokens::num)
         if (next_tok(t, p, le, b, en)) {
-            const int st = objnum::parse_double<BIG>(t + b, t + en, val);
+            const int st = objnum::parse_double<BIG>(TextIt{&t, b}, TextIt{&t, en}, val);
             if (st == objnum::NUM_DEFER) deferred = true;
             else if (st == objnum::NUM_UNSUPPORTED) report(status, line, OBJ_ERR_NUMBER);
         }
@@ -127,14 +186,17 @@ __device__ __forceinline__ void parse_numbers(const char* __restrict__ t, unsign
 }
 
 template <bool BIG>
-__global__ void __launch_bounds__(128) obj_parse_kernel(const char* __restrict__ t, unsigned n, unsigned n_chunks, const ObjCounts* __restrict__ base,
+__global__ void __launch_bounds__(128) obj_parse_kernel(const char* __restrict__ text, unsigned n, unsigned n_chunks, const ObjCounts* __restrict__ base,
                                                         unsigned char* __restrict__ defer, double* __restrict__ v, double* __restrict__ vn,
                                                         double* __restrict__ vt, int* __restrict__ fidx, unsigned* __restrict__ f_um,
                                                         unsigned* __restrict__ f_off, unsigned* __restrict__ um_off, unsigned* __restrict__ um_len,
                                                         unsigned long long* __restrict__ status) {
+    __shared__ unsigned smem[OBJ_SMEM_WORDS];
     const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= n_chunks) return;
-    if (BIG && !defer[c]) return;
+    const bool mine = c < n_chunks && (!BIG || defer[c]);
+    if (BIG && !__syncthreads_or(mine)) return;         // no chunk of this block asked for the 896-bit pass
+    const TextView t = stage_text(text, n, smem);
+    if (!mine) return;
     ObjCounts k = base[c];
     const unsigned c0 = c * OBJ_CHUNK, c1 = c0 + OBJ_CHUNK;
     unsigned s = first_line_start(t, c0, c1, n);
@@ -160,7 +222,7 @@ __global__ void __launch_bounds__(128) obj_parse_kernel(const char* __restrict__
             else {
                 for (int cnr = 0; cnr < 3; cnr++) {
                     long long idx[3];
-                    parse_corner(t + b[cnr], t + en[cnr], idx);
+                    parse_corner(t, b[cnr], en[cnr], idx);
                     if (idx[0] < 0 || idx[0] >= (long long)k.v || idx[1] < 0 || idx[1] >= (long long)k.vn || idx[2] < 0 || idx[2] >= (long long)k.vt) ok = false;
                     else { o[3 * cnr] = (int)idx[0]; o[3 * cnr + 1] = (int)idx[1]; o[3 * cnr + 2] = (int)idx[2]; }
                 }

@@ -191,9 +191,9 @@ MCPT_HD inline char lower(char c) { return (c >= 'A' && c <= 'Z') ? (char)(c + 3
 
 // atof of the token [p, end) (no blanks inside).  BIG = false: numbers that need the 896-bit path return NUM_DEFER
 // (value untouched); BIG = true: they are converted.  NUM_UNSUPPORTED: glibc would read this token differently.
-template <bool BIG>
-MCPT_HD inline int parse_double(const char* p, const char* end, double& value) {
-    const char* const tok = p;
+// It: a random-access iterator over chars (const char* on the host; the staged-text iterator of obj_ingest.cu on the device).
+template <bool BIG, class It>
+MCPT_HD inline int parse_double(It p, const It end, double& value) {
     bool neg = false;
     if (p < end && (*p == '+' || *p == '-')) { neg = *p == '-'; p++; }
     if (end - p >= 3) {
@@ -201,7 +201,7 @@ MCPT_HD inline int parse_double(const char* p, const char* end, double& value) {
         if ((a == 'i' && b == 'n' && c == 'f') || (a == 'n' && b == 'a' && c == 'n')) return NUM_UNSUPPORTED;
     }
     if (end - p >= 2 && p[0] == '0' && lower(p[1]) == 'x') return NUM_UNSUPPORTED;
-    const char* const mant = p;
+    const It mant = p;
     u64 w = 0;
     int nd = 0, e10 = 0;
     bool any = false, dropped = false;
@@ -222,7 +222,7 @@ MCPT_HD inline int parse_double(const char* p, const char* end, double& value) {
     }
     if (!any) { value = 0.0; return NUM_OK; }          // no conversion: atof returns +0
     if (p < end && (*p == 'e' || *p == 'E')) {
-        const char* r = p + 1;
+        It r = p + 1;
         bool eneg = false;
         if (r < end && (*r == '+' || *r == '-')) { eneg = *r == '-'; r++; }
         if (r < end && is_digit(*r)) {
@@ -248,7 +248,7 @@ MCPT_HD inline int parse_double(const char* p, const char* end, double& value) {
     Big N;
     big_set(N, 0);
     nd = 0; e10 = 0;
-    const char* s = mant;
+    It s = mant;
     bool frac = false;
     for (; s < end; s++) {
         if (*s == '.') { if (frac) break; frac = true; continue; }
@@ -259,7 +259,7 @@ MCPT_HD inline int parse_double(const char* p, const char* end, double& value) {
         else { if (d != 0) return NUM_UNSUPPORTED; if (!frac) e10++; }
     }
     if (s < end && (*s == 'e' || *s == 'E')) {
-        const char* r = s + 1;
+        It r = s + 1;
         bool eneg = false;
         if (r < end && (*r == '+' || *r == '-')) { eneg = *r == '-'; r++; }
         if (r < end && is_digit(*r)) {
@@ -268,13 +268,13 @@ MCPT_HD inline int parse_double(const char* p, const char* end, double& value) {
             e10 += eneg ? -ex : ex;
         }
     }
-    (void)tok;
     value = scale_big(N, e10, neg);
     return NUM_OK;
 }
 
 // atol of [p, end): optional sign, digits; saturates far outside any valid index
-MCPT_HD inline long long parse_long(const char* p, const char* end) {
+template <class It>
+MCPT_HD inline long long parse_long(It p, const It end) {
     bool neg = false;
     if (p < end && (*p == '+' || *p == '-')) { neg = *p == '-'; p++; }
     long long v = 0;

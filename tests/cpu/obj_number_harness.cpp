@@ -10,11 +10,11 @@ int main() {
     std::string tok;
     while (std::getline(std::cin, tok)) {
         double a = 0.0, b = 0.0;
-        const int sa = mcpt::objnum::parse_double<false>(tok.data(), tok.data() + tok.size(), a);
-        const int sb = mcpt::objnum::parse_double<true>(tok.data(), tok.data() + tok.size(), b);
+        const int sa = mcpt::objnum::parse_double<false, const char*>(tok.data(), tok.data() + tok.size(), a);
+        const int sb = mcpt::objnum::parse_double<true, const char*>(tok.data(), tok.data() + tok.size(), b);
         unsigned long long ua, ub;
         std::memcpy(&ua, &a, 8); std::memcpy(&ub, &b, 8);
-        std::printf("%d %016llx %d %016llx %lld\n", sa, ua, sb, ub, mcpt::objnum::parse_long(tok.data(), tok.data() + tok.size()));
+        std::printf("%d %016llx %d %016llx %lld\n", sa, ua, sb, ub, mcpt::objnum::parse_long<const char*>(tok.data(), tok.data() + tok.size()));
     }
     return 0;
 }
