@@ -157,7 +157,7 @@ MCPT_API int mcpt_upload_scene(mcpt_ctx* ctx, const mcpt_scene_desc* scene);
  * does not (hex floats, inf/nan, > 40 significant digits).  ms_out (may be NULL) = device time incl. the H2D copy. */
 MCPT_API int mcpt_ingest_obj(mcpt_ctx* ctx, const char* obj_text, int64_t n_bytes, const mcpt_scene_desc* tables,
                              const char* const* material_names, float* ms_out);
-/* The same, reading `file` itself: 8 MiB blocks through a pinned ring, each block's H2D copy overlapping the next read. */
+/* The same, reading `file` itself: 8 MiB blocks read by 4 threads into a pinned ring, the H2D copies overlapping the reads. */
 MCPT_API int mcpt_ingest_obj_file(mcpt_ctx* ctx, const char* file, const mcpt_scene_desc* tables,
                                   const char* const* material_names, float* ms_out);
 /* read_scene (MTPC/sceneManagement.cpp:264-274) with the OBJ on the GPU: <path><name>.mtl and .camera are parsed on the

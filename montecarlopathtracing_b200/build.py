@@ -19,6 +19,7 @@ CXX = os.environ.get("MCPT_CXX", "/usr/bin/g++")  # not $CXX: the image exports 
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-ccbin", CXX, "-Xcompiler", "-fPIC,-fvisibility=hidden"]
+NVCC_FLAGS += os.environ.get("MCPT_NVCC_EXTRA", "").split()   # developer knob for A/B builds (e.g. -DMCPT_SHADE_MIN_CTAS=5)
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall"]
 
 CU_SOURCES = {"lbvh.cu": ["--fmad=false"], "ploc.cu": [], "render.cu": [], "wavefront.cu": [], "png_device.cu": [], "obj_ingest.cu": [], "api.cu": []}
