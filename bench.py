@@ -305,7 +305,7 @@ def run_ours(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": ("synthetic mesh (montecarlopathtracing_b200/synthetic.py, seed 1234)" if scene_name.startswith("synthetic")
                                                                else "shipped scene (scenes/%s.obj)" % scene_name),
             "config": {"workload": args.workload, "scene": scene_name, "width": w, "height": h, "spp_total": spp,
-                       "spp_per_gpu": spp_per_gpu, "mode": args.mode, "partition": "spp-split, 8 chunks, fixed-tree sum",
+                       "spp_per_gpu": spp_per_gpu, "mode": args.mode, "partition": "spp-split, 64 chunks, fixed-tree sum",
                        "l2_policy": "no flush: the scene (%.1f MB of nodes+triangles) is L1/L2-resident by design and every "
                                     "launch re-reads it millions of times; the wavefront state and ray queues (~%d MB) "
                                     "exceed L2 at this size" % ((32 + 48 + 64) * n_faces / 1e6, int(w * h * (100 + 16 * n_lights + 32 * (n_lights + 1)) / 1e6))},

@@ -106,8 +106,11 @@ enum { MCPT_MODE_MEGAKERNEL = 0, MCPT_MODE_WAVEFRONT = 1 };
 enum { MCPT_FLAG_COUNT = 1,            /* count node visits / triangle tests (slower) */
        MCPT_FLAG_NO_PRIMARY_REUSE = 2  /* re-trace the (identical, Q4) primary ray for every sample */ };
 
-/* Number of sample chunks a render is always cut into; GPU r of R owns chunks [r*C/R,(r+1)*C/R). */
-#define MCPT_NUM_CHUNKS 8
+/* Number of sample chunks a render is always cut into (chunk k = samples [k*spp/C, (k+1)*spp/C)); GPU r of R in
+ * {1,2,4,8} owns chunks [r*C/R,(r+1)*C/R).  Every chunk is accumulated sequentially into its own plane and the planes are
+ * summed by one fixed pairwise tree, so the image depends on neither the GPU count nor on how many chunks one thread (or
+ * wavefront slot) integrates — which is what lets the integrator pick its degree of parallelism per workload. */
+#define MCPT_NUM_CHUNKS 64
 
 /* ---- host side: the kept C++ shell (loaders, render_scene, PNG) ---------------------------- */
 

@@ -5,7 +5,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libmcpt.so")
 
-NUM_CHUNKS = 8
+NUM_CHUNKS = 64
 MODE_MEGAKERNEL, MODE_WAVEFRONT = 0, 1
 FLAG_COUNT, FLAG_NO_PRIMARY_REUSE = 1, 2
 

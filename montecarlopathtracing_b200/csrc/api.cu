@@ -44,6 +44,7 @@ struct mcpt_ctx {
     void* d_io = nullptr; size_t io_cap = 0;            // scratch: rays in / hits out of mcpt_trace
     char* d_text = nullptr; size_t text_cap = 0;        // scratch: OBJ text of mcpt_ingest_obj
     DevArena ingest_text, ingest_stmt;                  // scratch: ingest temporaries
+    DevArena scene_arena, tables_arena;                 // grow-only: a re-upload of a scene that fits allocates nothing
     char* h_pin[PIN_RING] = {}; cudaEvent_t pin_ev[PIN_RING] = {};   // pinned ring of mcpt_ingest_obj_file (one buffer per reader thread)
     int last_ingest_launches = 0;
     float last_build_ms = 0.f;
@@ -71,12 +72,8 @@ template <class T> cudaError_t grow(T*& p, size_t& cap, size_t bytes) {
     if (e == cudaSuccess) cap = bytes;
     return e;
 }
-void free_scene(mcpt_ctx* c) {
-    SceneBuffers& s = c->sb;
-    cudaFree(s.arena);
-    s = SceneBuffers();
-    cudaFree(c->d_materials); cudaFree(c->d_textures); cudaFree(c->d_tex_bytes); cudaFree(c->d_lights);
-    cudaFree(c->d_light_tris); cudaFree(c->d_light_cdf);
+void free_scene(mcpt_ctx* c) {   // forgets the scene; the arenas stay (released by mcpt_destroy)
+    c->sb = SceneBuffers();
     c->d_materials = nullptr; c->d_textures = nullptr; c->d_tex_bytes = nullptr; c->d_lights = nullptr;
     c->d_light_tris = nullptr; c->d_light_cdf = nullptr;
     c->scene_loaded = false;
@@ -140,7 +137,7 @@ int alloc_scene(mcpt_ctx* c, int n) {
         carve(s.nodes2, N); carve(s.cl_lo[0], N); carve(s.cl_lo[1], N); carve(s.cl_hi[0], N); carve(s.cl_hi[1], N);
         carve(s.ploc_nn, N); carve(s.ploc_flag, N); carve(s.ploc_scan, N);
         carve_bytes(s.ploc_temp, s.ploc_temp_bytes); carve_bytes(s.ploc_state, 64); carve_bytes(s.cub_temp, s.cub_temp_bytes);
-        if (pass == 0) { CU(cudaMalloc((void**)&base, used)); s.arena = base; }
+        if (pass == 0) { CU(c->scene_arena.reserve(used)); base = c->scene_arena.base; s.arena = base; }
     }
     return MCPT_OK;
 }
@@ -201,8 +198,21 @@ int upload_tables(mcpt_ctx* c, const mcpt_scene_desc* d, const std::vector<std::
         L.n_search = m < L.count ? m + 1 : L.count;
     }
     c->n_materials = d->n_materials; c->n_textures = d->n_textures; c->n_lights = d->n_lights;
-    CU(dev_alloc(c->d_materials, mats.size())); CU(dev_alloc(c->d_textures, texs.size())); CU(dev_alloc(c->d_tex_bytes, tex_bytes.size()));
-    CU(dev_alloc(c->d_lights, lights.size())); CU(dev_alloc(c->d_light_tris, ltris.size())); CU(dev_alloc(c->d_light_cdf, cdf.size()));
+    {
+        char* base = nullptr;
+        size_t used = 0;
+        auto carve = [&](auto*& p, size_t count) {
+            using T = std::remove_reference_t<decltype(*p)>;
+            if (base) p = (T*)(base + used);
+            used += (sizeof(T) * (count ? count : 1) + 255) & ~(size_t)255;
+        };
+        for (int pass = 0; pass < 2; pass++) {
+            used = 0;
+            carve(c->d_materials, mats.size()); carve(c->d_textures, texs.size()); carve(c->d_tex_bytes, tex_bytes.size());
+            carve(c->d_lights, lights.size()); carve(c->d_light_tris, ltris.size()); carve(c->d_light_cdf, cdf.size());
+            if (pass == 0) { CU(c->tables_arena.reserve(used)); base = c->tables_arena.base; }
+        }
+    }
     CU(cudaMemcpyAsync(c->d_materials, mats.data(), sizeof(DMaterial) * mats.size(), cudaMemcpyHostToDevice, st));
     if (!texs.empty()) CU(cudaMemcpyAsync(c->d_textures, texs.data(), sizeof(DTexture) * texs.size(), cudaMemcpyHostToDevice, st));
     if (!tex_bytes.empty()) CU(cudaMemcpyAsync(c->d_tex_bytes, tex_bytes.data(), tex_bytes.size(), cudaMemcpyHostToDevice, st));
@@ -269,14 +279,15 @@ int ingest_resident(mcpt_ctx* c, int64_t n_bytes, const mcpt_scene_desc* d, cons
         std::vector<int> idx;
         for (int i = 0; i < n; i++) if (mat[i] == d->lights[l].mat_id) idx.push_back(i);
         if (idx.empty()) continue;
-        int* d_idx = nullptr; double* d_out = nullptr;
-        CU(dev_alloc(d_idx, idx.size())); CU(dev_alloc(d_out, 18 * idx.size()));
+        // the parsed statements are dead after the flatten: their arena doubles as the gather's scratch
+        const size_t out_off = (4 * idx.size() + 255) & ~(size_t)255;
+        CU(c->ingest_stmt.reserve(out_off + 144 * idx.size()));
+        int* d_idx = (int*)c->ingest_stmt.base; double* d_out = (double*)(c->ingest_stmt.base + out_off);
         CU(cudaMemcpyAsync(d_idx, idx.data(), 4 * idx.size(), cudaMemcpyHostToDevice, st));
         e = launch_gather_faces(d_idx, (int)idx.size(), s.pos, s.nrm, d_out, st);
         std::vector<double> packed(18 * idx.size());
         if (!e) e = (int)cudaMemcpyAsync(packed.data(), d_out, 8 * packed.size(), cudaMemcpyDeviceToHost, st);
         if (!e) e = (int)cudaStreamSynchronize(st);
-        cudaFree(d_idx); cudaFree(d_out);
         if (e) return fail_cuda((cudaError_t)e, "gather light faces");
         lpos[l].resize(9 * idx.size()); lnrm[l].resize(9 * idx.size());
         for (size_t j = 0; j < idx.size(); j++) {
@@ -318,7 +329,7 @@ MCPT_API int mcpt_create(int device, mcpt_ctx** out) {
     CU(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
     c->stream = c->own_stream;
     CU(cudaEventCreate(&c->ev0)); CU(cudaEventCreate(&c->ev1)); CU(cudaEventCreate(&c->ev2)); CU(cudaEventCreate(&c->ev3));
-    CU(dev_alloc(c->d_counters, 4));
+    CU(dev_alloc(c->d_counters, 8));
     *out = c;
     return MCPT_OK;
 }
@@ -328,7 +339,7 @@ MCPT_API void mcpt_destroy(mcpt_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     free_scene(c);
-    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); cudaFree(c->d_png); cudaFree(c->d_text); c->ingest_text.release(); c->ingest_stmt.release(); c->wfh.destroy();
+    cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); cudaFree(c->d_png); cudaFree(c->d_text); c->ingest_text.release(); c->ingest_stmt.release(); c->scene_arena.release(); c->tables_arena.release(); c->wfh.destroy();
     for (int k = 0; k < PIN_RING; k++) { if (c->h_pin[k]) cudaFreeHost(c->h_pin[k]); if (c->pin_ev[k]) cudaEventDestroy(c->pin_ev[k]); }
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->own_stream);
@@ -566,12 +577,22 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
     if (launches) *launches += 1;
     P.spp = spp; P.chunk_begin = cb; P.n_chunks = nch;
     // enough threads to fill 148 SMs several times over, otherwise as many samples per thread as possible
+    // Degree of parallelism = pixels x (chunks / chunks per thread).  Megakernel: enough threads to fill 148 SMs several
+    // times over.  Wavefront: enough path slots that one wf_trace launch carries ~2 M rays per pipe (a slot emits one
+    // extension ray and one shadow ray per light and iteration): with fewer, a launch is mostly its drain phase — the
+    // queue is empty and every warp waits for its longest ray — and cornell-box at 1024^2 ran 28 % slower.
     int g = nch;
-    while (g > 1 && (long long)width * height * (nch / g) < 600000LL) g >>= 1;
+    long long want = 600000LL;
+    if (mode == MCPT_MODE_WAVEFRONT) {
+        const char* v = getenv("MCPT_WF_SLOTS");
+        want = v && *v ? atoll(v) : std::max(600000LL, 6000000LL / (c->n_lights + 1));
+        if (want > (1LL << 25)) want = 1LL << 25;
+    }
+    while (g > 1 && (long long)width * height * (nch / g) < want) g >>= 1;
     P.chunks_per_thread = g;
     P.seed_lo = (unsigned)c->seed; P.seed_hi = (unsigned)(c->seed >> 32);
     P.planes = c->d_planes; P.counters = c->d_counters;
-    CU(cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), c->stream));
+    CU(cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
     CU(cudaEventRecord(c->ev3, c->stream));
     if (mode == MCPT_MODE_WAVEFRONT) {
         const int n_slots = wavefront_slots(P);
@@ -615,7 +636,7 @@ MCPT_API int mcpt_trace_device(mcpt_ctx* c, const float* d_org_dir, int n, mcpt_
     if (!c || !c->sb.built) return fail_arg("mcpt_trace: build the BVH first");
     if (n < 0 || (n > 0 && (!d_org_dir || !d_hits))) return fail_arg("mcpt_trace: bad buffers");
     CU(cudaSetDevice(c->device));
-    CU(cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(unsigned long long), c->stream));
+    CU(cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
     CU(cudaEventRecord(c->ev0, c->stream));
     const int e = launch_trace(device_scene(c), d_org_dir, n, d_hits, (flags & MCPT_FLAG_COUNT) != 0, c->d_counters, c->stream);
     if (e) return fail_cuda((cudaError_t)e, "trace_kernel launch");
@@ -662,8 +683,8 @@ MCPT_API int mcpt_render_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, 
     int rc = check_render_args(c, cam, width, height, spp);
     if (rc) return rc;
     const int nch = ce - cb;
-    if (cb < 0 || ce > MCPT_NUM_CHUNKS || !(nch == 1 || nch == 2 || nch == 4 || nch == 8) || cb % nch != 0)
-        return fail_arg("mcpt_render_chunks: [chunk_begin, chunk_end) must be an aligned power-of-two range within 0..8");
+    if (cb < 0 || ce > MCPT_NUM_CHUNKS || nch < 1 || (nch & (nch - 1)) != 0 || cb % nch != 0)
+        return fail_arg("mcpt_render_chunks: [chunk_begin, chunk_end) must be an aligned power-of-two range within 0..MCPT_NUM_CHUNKS");
     if (!d_partial) return fail_arg("mcpt_render_chunks: null output");
     CU(cudaSetDevice(c->device));
     int launches = 0;
@@ -701,9 +722,14 @@ static int render_device(mcpt_ctx* c, const mcpt_camera* cam, int width, int hei
 static int finish_render_stats(mcpt_ctx* c, mcpt_stats* st, int width, int height, int spp, int launches) {
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
-    unsigned long long cnt[4];
+    unsigned long long cnt[8];
     CU(cudaMemcpy(cnt, c->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
     fill_stats(c, st, (double)width * height * (double)spp, cnt, ms, launches);
+    if (cnt[3] && getenv("MCPT_DIAG"))   // wavefront + MCPT_FLAG_COUNT: how full the warps are when they issue the two step kinds
+        std::fprintf(stderr, "[diag] node steps: %.2f lanes per warp issue (%llu issues); triangle tests: %.2f lanes per issue (%llu); "
+                     "%.2f node issues and %.3f tri issues per loop iteration (%llu iterations)\n",
+                     (double)cnt[1] / (double)cnt[3], cnt[3], cnt[4] ? (double)cnt[2] / (double)cnt[4] : 0.0, cnt[4],
+                     (double)cnt[3] / (double)cnt[5], (double)cnt[4] / (double)cnt[5], cnt[5]);
     return fill_kernel_times(c, st);
 }
 

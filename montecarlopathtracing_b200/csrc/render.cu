@@ -272,6 +272,9 @@ int launch_sum_planes(const float* d_planes, int n, long long count, float scale
         case 2: sum_planes_kernel<2><<<blocks, tpb, 0, stream>>>(d_planes, count, scale, d_out); break;
         case 4: sum_planes_kernel<4><<<blocks, tpb, 0, stream>>>(d_planes, count, scale, d_out); break;
         case 8: sum_planes_kernel<8><<<blocks, tpb, 0, stream>>>(d_planes, count, scale, d_out); break;
+        case 16: sum_planes_kernel<16><<<blocks, tpb, 0, stream>>>(d_planes, count, scale, d_out); break;
+        case 32: sum_planes_kernel<32><<<blocks, tpb, 0, stream>>>(d_planes, count, scale, d_out); break;
+        case 64: sum_planes_kernel<64><<<blocks, tpb, 0, stream>>>(d_planes, count, scale, d_out); break;
         default: return (int)cudaErrorInvalidValue;
     }
     return (int)cudaGetLastError();

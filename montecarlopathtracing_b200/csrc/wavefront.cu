@@ -263,6 +263,7 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
     unsigned n_nodes = 0, n_tris = 0;
+    unsigned w_node = 0, w_tri = 0, w_iter = 0;   // COUNT only: warp-level issues of node steps / triangle tests / loop iterations
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[0], (unsigned long long)n);
     RayCtx r = ray_setup(f3(0.f, 0.f, 0.f), f3(1.f, 1.f, 1.f), sc.qgrid);
     Hit best; best.t = 0.f; best.u = 0.f; best.v = 0.f; best.k = -1;
@@ -309,6 +310,7 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
         }
         // a lane that arrives at a leaf parks it and keeps walking: the triangle test is issued when enough lanes hold one
         for (int k = 0; k < node_steps; k++) {
+            if (COUNT) { if (__any_sync(0xffffffffu, node >= 0) && lane == 0) w_node++; }
             if (node >= 0) node_step<COUNT>(sc.qnodes, node, r, best.t, stack, sp, n_nodes);
             if (node < 0 && node != MCPT_SENT && pend == 0) { pend = node; node = stack[--sp]; }
         }
@@ -316,6 +318,7 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
         const bool blocked = has_p && node < 0;   // a second leaf, or nothing left but the parked one
         const unsigned pm = __ballot_sync(0xffffffffu, has_p), bm = __ballot_sync(0xffffffffu, blocked);
         const unsigned nm = __ballot_sync(0xffffffffu, node >= 0);
+        if (COUNT && lane == 0) { w_iter++; if (pm != 0u && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) w_tri++; }
         if (has_p && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) {
             tri_test<COUNT>(sc.tri, ~pend, r, best, n_tris);
             pend = 0;
@@ -324,7 +327,10 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
     if (has_ray) write_back();
     if (COUNT) {
         const unsigned a = __reduce_add_sync(0xffffffffu, n_nodes), b = __reduce_add_sync(0xffffffffu, n_tris);
-        if (lane == 0) { atomicAdd(&stats[1], (unsigned long long)a); atomicAdd(&stats[2], (unsigned long long)b); }
+        if (lane == 0) {
+            atomicAdd(&stats[1], (unsigned long long)a); atomicAdd(&stats[2], (unsigned long long)b);
+            atomicAdd(&stats[3], (unsigned long long)w_node); atomicAdd(&stats[4], (unsigned long long)w_tri); atomicAdd(&stats[5], (unsigned long long)w_iter);
+        }
     }
 }
 

@@ -1,7 +1,7 @@
 """SPP-split rendering over R ranks (one process per GPU, torch.distributed for the plumbing).
 
-The spp samples are always cut into NUM_CHUNKS = 8 chunks in sample-index order.  Rank r of R in {1,2,4,8} integrates
-chunks [r*8/R, (r+1)*8/R) and leaves their fixed pairwise-tree SUM in one float buffer (mcpt_render_chunks); the R
+The spp samples are always cut into NUM_CHUNKS = 64 chunks in sample-index order.  Rank r of R in {1,2,4,8} integrates
+chunks [r*64/R, (r+1)*64/R) and leaves their fixed pairwise-tree SUM in one float buffer (mcpt_render_chunks); the R
 buffers are gathered to rank 0 — the path's only exchange — and summed there by the same pairwise tree
 (mcpt_sum_partials), then scaled by 1/spp.  The association of the float additions is therefore identical for every
 R, and since Philox is keyed by (pixel, sample) the 1-, 2-, 4- and 8-GPU images are bit-identical.  ncclReduce is NOT
