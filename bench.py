@@ -29,8 +29,9 @@ WORKLOADS = {
     "synthetic-1M-1920x1080-spp64": ("synthetic-1M", 1920, 1080, 64),
 }
 # DRAM bytes of ONE launch of the dominant kernel from the committed `ncu --set full` capture (bytes; per launch like
-# roofline.achieved).  ~21 MB against ~180 MB of algorithmic node+triangle bytes per launch: the scene is served from L1/L2.
-NCU_TRAFFIC = {("cornell-box-1024x1024-spp256", "wavefront"): 20.585984e6 + 0.553984e6,
+# roofline.achieved).  ~89 MB (ray queue in, hit records out) against ~1.4 GB of algorithmic node+triangle bytes per launch: the
+# scene is served from L1/L2.
+NCU_TRAFFIC = {("cornell-box-1024x1024-spp256", "wavefront"): 79.893504e6 + 9.083136e6,
                ("cornell-box-1024x1024-spp256", "megakernel"): 6.414592e6 + 64.855552e6}
 SYNTHETIC_TRIS = {"synthetic-5M": 5_000_000, "synthetic-1M": 1_000_000}
 DEFAULT_WORKLOAD = "cornell-box-1024x1024-spp256"
@@ -320,7 +321,7 @@ def run_ours(args):
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
-                         "traffic": NCU_TRAFFIC.get((args.workload, args.mode)), "traffic_source": "profiles/r1_wavefront_final_ncu.md "
+                         "traffic": NCU_TRAFFIC.get((args.workload, args.mode)), "traffic_source": "profiles/r1_final_wf_trace_ncu.md "
                          "(dram__bytes_read.sum + dram__bytes_write.sum of one mid-render wf_trace launch; null for workloads not captured)",
                          "peak_source": pk_src, "kernel": kernel, "kernel_ms": k_ms, "launches_per_step": n_k,
                          "kernel_ms_per_step": k_ms_step, "integrator_ms_per_step": sum(integ_ms) / len(integ_ms),

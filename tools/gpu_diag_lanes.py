@@ -12,4 +12,5 @@ ctx.render(s.camera, 8, w, h)
 ctx.render(s.camera, spp, w, h)
 st = ctx.last_stats
 print("%s spp %d: integrate %.2f ms, %.1f Msamples/s, %.1f Mrays/s, %d trace launches" % (name, spp, st.integrate_ms, st.samples / st.render_ms * 1e-3, st.rays / st.render_ms * 1e-3, st.trace_launches), flush=True)
-ctx.render(s.camera, spp, w, h, flags=M.FLAG_COUNT)
+if os.environ.get("MCPT_DIAG"):
+    ctx.render(s.camera, spp, w, h, flags=M.FLAG_COUNT)

@@ -1,5 +1,5 @@
 """Run under torchrun on N GPUs: the SPP-split render gathered to rank 0 must be BIT-identical to rank 0's own
-single-GPU mcpt_render of all 8 chunks.  Prints one line; exit code 1 on mismatch."""
+single-GPU mcpt_render of all 64 chunks.  Prints one line; exit code 1 on mismatch."""
 import os
 import sys
 
