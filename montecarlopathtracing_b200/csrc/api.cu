@@ -729,7 +729,10 @@ static int finish_render_stats(mcpt_ctx* c, mcpt_stats* st, int width, int heigh
         std::fprintf(stderr, "[diag] node steps: %.2f lanes per warp issue (%llu issues); triangle tests: %.2f lanes per issue (%llu); "
                      "%.2f node issues and %.3f tri issues per loop iteration (%llu iterations)\n",
                      (double)cnt[1] / (double)cnt[3], cnt[3], cnt[4] ? (double)cnt[2] / (double)cnt[4] : 0.0, cnt[4],
-                     (double)cnt[3] / (double)cnt[5], (double)cnt[4] / (double)cnt[5], cnt[5]);
+                     (double)cnt[3] / (double)cnt[5], (double)cnt[4] / (double)cnt[5], cnt[5]),
+        std::fprintf(stderr, "[diag] per node-step issue: %.2f lanes idle (no ray), %.2f finished but holding a parked leaf, %.2f at a second leaf\n",
+                     (double)cnt[6] / (double)cnt[3], (double)cnt[7] / (double)cnt[3],
+                     32.0 - ((double)cnt[1] + (double)cnt[6] + (double)cnt[7]) / (double)cnt[3]);
     return fill_kernel_times(c, st);
 }
 

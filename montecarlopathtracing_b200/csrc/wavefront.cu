@@ -250,6 +250,11 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
 // from the queue head with one atomic for the warp.  Every loop iteration is one traversal step per lane: lanes at
 // an internal node take a node step; lanes at a leaf take a leaf step once `leaf_min` lanes have gathered there (or
 // no lane is at a node), so the triangle test is not issued for one or two lanes at a time.
+// Two parked leaves per lane instead of one: measured SLOWER (cornell-box 1465 -> 1396, veach-mis 680 -> 647 Msamples/s): lanes
+// at an internal node per issue rise only 13.6 -> 13.9, the extra bookkeeping costs more.  Kept as an A/B switch.
+#ifndef MCPT_PEND2
+#define MCPT_PEND2 0
+#endif
 #ifndef MCPT_TRACE_MIN_CTAS
 #define MCPT_TRACE_MIN_CTAS 8
 #endif
@@ -263,6 +268,7 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
     unsigned n_nodes = 0, n_tris = 0;
+    unsigned w_idle = 0, w_fin = 0;
     unsigned w_node = 0, w_tri = 0, w_iter = 0;   // COUNT only: warp-level issues of node steps / triangle tests / loop iterations
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[0], (unsigned long long)n);
     RayCtx r = ray_setup(f3(0.f, 0.f, 0.f), f3(1.f, 1.f, 1.f), sc.qgrid);
@@ -281,6 +287,9 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
         }
     };
     int pend = 0;   // postponed leaf (negative ~k), 0 = none
+#if MCPT_PEND2
+    int pend2 = 0;  // a second one: leaves come in pairs (siblings), and a lane stuck at its second leaf walks no further
+#endif
     while (true) {
         const bool idle = node == MCPT_SENT && pend == 0;
         const unsigned im = __ballot_sync(0xffffffffu, idle);
@@ -310,9 +319,19 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
         }
         // a lane that arrives at a leaf parks it and keeps walking: the triangle test is issued when enough lanes hold one
         for (int k = 0; k < node_steps; k++) {
-            if (COUNT) { if (__any_sync(0xffffffffu, node >= 0) && lane == 0) w_node++; }
+            if (COUNT) {
+                const unsigned at_node = __ballot_sync(0xffffffffu, node >= 0);
+                const unsigned idle_m = __ballot_sync(0xffffffffu, node == MCPT_SENT && pend == 0);
+                const unsigned fin_m = __ballot_sync(0xffffffffu, node == MCPT_SENT && pend != 0);
+                if (at_node != 0u && lane == 0) { w_node++; w_idle += __popc(idle_m); w_fin += __popc(fin_m); }
+            }
             if (node >= 0) node_step<COUNT>(sc.qnodes, node, r, best.t, stack, sp, n_nodes);
-            if (node < 0 && node != MCPT_SENT && pend == 0) { pend = node; node = stack[--sp]; }
+            if (node < 0 && node != MCPT_SENT) {
+                if (pend == 0) { pend = node; node = stack[--sp]; }
+#if MCPT_PEND2
+                else if (pend2 == 0) { pend2 = node; node = stack[--sp]; }
+#endif
+            }
         }
         const bool has_p = pend != 0;
         const bool blocked = has_p && node < 0;   // a second leaf, or nothing left but the parked one
@@ -321,7 +340,11 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
         if (COUNT && lane == 0) { w_iter++; if (pm != 0u && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) w_tri++; }
         if (has_p && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) {
             tri_test<COUNT>(sc.tri, ~pend, r, best, n_tris);
+#if MCPT_PEND2
+            pend = pend2; pend2 = 0;
+#else
             pend = 0;
+#endif
         }
     }
     if (has_ray) write_back();
@@ -330,6 +353,7 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
         if (lane == 0) {
             atomicAdd(&stats[1], (unsigned long long)a); atomicAdd(&stats[2], (unsigned long long)b);
             atomicAdd(&stats[3], (unsigned long long)w_node); atomicAdd(&stats[4], (unsigned long long)w_tri); atomicAdd(&stats[5], (unsigned long long)w_iter);
+            atomicAdd(&stats[6], (unsigned long long)w_idle); atomicAdd(&stats[7], (unsigned long long)w_fin);
         }
     }
 }
