@@ -80,7 +80,7 @@ def test_deterministic_and_seed_dependent(gpu_ctx, scenes):
 def test_image_independent_of_gpu_count(gpu_ctx, scenes, w, h, spp):
     """R virtual ranks (R = 1,2,4,8) run one after another on this GPU: each integrates its chunk range into a partial
     buffer, the partials are tree-summed as rank 0 would after the gather.  All four images must be BIT-identical to
-    mcpt_render's.  Covers spp < 8 (empty chunks), spp not divisible by 8, sizes that are not tile multiples and a
+    mcpt_render's.  Covers spp < 64 (empty chunks), spp not divisible by 64, sizes that are not tile multiples and a
     size large enough that a thread owns several chunks."""
     import torch
     from montecarlopathtracing_b200.multigpu import chunk_range, gpu_backend
@@ -223,3 +223,21 @@ def test_render_png_equals_render_then_write(gpu_ctx, scenes, tmp_path):
     M.write_png(g, img)
     assert open(f, "rb").read() == open(g, "rb").read()
     assert st.samples == 300 * 225 * 4 and np.asarray(Image.open(f)).shape == (225, 300, 3)
+
+
+@pytest.mark.parametrize("name,w,h,spp", [("cornell-box", 200, 120, 37), ("veach-mis", 160, 120, 70), ("cornell-box", 96, 64, 200)])
+def test_image_independent_of_the_number_of_path_slots(gpu_ctx, scenes, name, w, h, spp, monkeypatch):
+    """The wavefront integrator picks how many chunks a path slot integrates (api.cu enqueue_chunks: ~2 M rays per launch);
+    MCPT_WF_SLOTS overrides the target.  One slot per pixel, the default and one slot per (pixel, chunk) must give the
+    same bits: the per-chunk planes and their fixed sum tree do not depend on the grouping."""
+    s = scenes[name]
+    _load(gpu_ctx, s)
+    gpu_ctx.set_seed(9)
+    base = gpu_ctx.render(s.camera, spp, w, h, mode=M.MODE_MEGAKERNEL)
+    for target in ("1", None, "1000000000"):
+        if target is None:
+            monkeypatch.delenv("MCPT_WF_SLOTS", raising=False)
+        else:
+            monkeypatch.setenv("MCPT_WF_SLOTS", target)
+        img = gpu_ctx.render(s.camera, spp, w, h, mode=M.MODE_WAVEFRONT)
+        assert np.array_equal(img.view(np.uint32), base.view(np.uint32)), "MCPT_WF_SLOTS=%s differs" % target
