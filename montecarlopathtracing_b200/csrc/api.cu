@@ -13,6 +13,7 @@
 #include <cstring>
 #include <string>
 #include <type_traits>
+#include <unordered_map>
 #include <vector>
 #include "lbvh.h"
 #include "render.h"
@@ -257,10 +258,14 @@ int ingest_resident(mcpt_ctx* c, int64_t n_bytes, const mcpt_scene_desc* d, cons
     std::vector<std::string> um_names;
     e = obj_ingest_names(g, um_names, st);
     if (e) return fail_cuda((cudaError_t)e, "obj_ingest_names");
+    std::unordered_map<std::string, int> by_name;
+    for (int m = 0; m < d->n_materials; m++)
+        if (names[m]) by_name[names[m]] = m;              // a repeated newmtl name keeps one entry (scene_loader.cpp)
     std::vector<int> um_mat(um_names.size(), -1);
-    for (size_t i = 0; i < um_names.size(); i++)
-        for (int m = 0; m < d->n_materials; m++)
-            if (names[m] && um_names[i] == names[m]) um_mat[i] = m;   // a repeated newmtl name keeps one entry (scene_loader.cpp)
+    for (size_t i = 0; i < um_names.size(); i++) {
+        const auto it = by_name.find(um_names[i]);
+        if (it != by_name.end()) um_mat[i] = it->second;
+    }
     lap("usemtl names");
     if (int rc = alloc_scene(c, (int)g.n_f)) return rc;
     lap("alloc_scene");
