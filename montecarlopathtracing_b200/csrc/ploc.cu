@@ -19,7 +19,9 @@
 
 namespace mcpt {
 
+#ifndef PLOC_RADIUS
 #define PLOC_RADIUS 8
+#endif
 #define PLOC_TPB 256
 #define PLOC_FINISH 1024
 
