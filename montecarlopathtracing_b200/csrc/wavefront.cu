@@ -17,6 +17,7 @@
 // vis[n_slots]; ray queue ray_o / ray_d of (n_lights + 1) * n_slots entries.
 #include <cstdlib>
 #include <vector>
+#include <cstdio>
 #include "render.h"
 #include "shade.cuh"
 
@@ -440,6 +441,7 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
     const int refill_min = env_int("MCPT_REFILL_MIN", 12), leaf_min = env_int("MCPT_LEAF_MIN", 12),
               block_min = env_int("MCPT_BLOCK_MIN", 4), node_steps = env_int("MCPT_NODE_STEPS", 4);
     const int batch = 8;
+    const bool diag = getenv("MCPT_DIAG_ALIVE") != nullptr;
     int nlaunch = 0, n_timed = 0;
     for (int b = 0;; b++) {
         bool any = false;
@@ -470,6 +472,7 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
                 if (pp[k].done) continue;
                 WF_CU(cudaEventSynchronize(H.events[2 + 2 * k + ((b - 1) & 1)]));
                 if (H.h_alive[2 * k + ((b - 1) & 1)] == 0u) pp[k].done = true;
+                if (diag && k == 0) std::fprintf(stderr, "[diag] pipe 0 after iteration %d: %u of %d slots alive\n", b * batch - 1, H.h_alive[2 * k + ((b - 1) & 1)], pp[k].B.slot_end - pp[k].B.slot_begin);
             }
         }
         if (b > (1 << 22)) return (int)cudaErrorUnknown;
