@@ -3,7 +3,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmcpt.so")
+LIB_PATH = os.environ.get("MCPT_LIB") or os.path.join(HERE, "libmcpt.so")   # MCPT_LIB: developer A/B builds (build.py MCPT_BUILD_TAG)
 
 NUM_CHUNKS = 64
 MODE_MEGAKERNEL, MODE_WAVEFRONT = 0, 1

@@ -11,8 +11,9 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 HOST = os.path.join(HERE, "host")
-OBJ = os.path.join(HERE, "build")
-LIB = os.path.join(HERE, "libmcpt.so")
+TAG = os.environ.get("MCPT_BUILD_TAG", "")   # developer knob: A/B builds live beside the product as libmcpt_<tag>.so
+OBJ = os.path.join(HERE, "build" + ("_" + TAG if TAG else ""))
+LIB = os.path.join(HERE, "libmcpt%s.so" % ("_" + TAG if TAG else ""))
 CLI = os.path.join(HERE, "mcpt_cli")
 NVCC = os.environ.get("MCPT_NVCC", "/usr/local/cuda/bin/nvcc")
 CXX = os.environ.get("MCPT_CXX", "/usr/bin/g++")  # not $CXX: the image exports a wrapper unusable for linking
@@ -69,7 +70,7 @@ def build(force=False, verbose=False):
     if force or jobs or not os.path.exists(LIB):
         _run([NVCC] + ARCH + ["-shared", "-ccbin", CXX, "-o", LIB] + objs + ["-cudart", "static"])
     cli_src = os.path.join(HOST, "mcpt_cli.cpp")
-    if os.path.exists(cli_src) and (force or _newer(CLI, [cli_src, LIB])):
+    if not TAG and os.path.exists(cli_src) and (force or _newer(CLI, [cli_src, LIB])):
         _run([CXX] + CXX_FLAGS + [cli_src, "-o", CLI, "-L" + HERE, "-lmcpt", "-Wl,-rpath,$ORIGIN"])
     return LIB
 

@@ -117,6 +117,7 @@ int alloc_scene(mcpt_ctx* c, int n) {
     s.ploc_temp_bytes = ploc_scan_temp_bytes(n);
     s.cub_temp_bytes = lbvh_sort_temp_bytes(n);
     { const char* v = getenv("MCPT_BVH"); s.use_ploc = !(v && std::strcmp(v, "lbvh") == 0); }
+    { const char* v = getenv("MCPT_LEAF_PAIRS"); s.fold_pairs = !(v && std::strcmp(v, "0") == 0); }
     // one allocation, carved (a scene of n faces needs ~30 arrays; 30 cudaMalloc/cudaFree pairs cost more than a small build)
     char* base = nullptr;
     size_t used = 0;

@@ -16,9 +16,13 @@ struct __align__(16) BvhNode { float4 q[4]; };
 
 // Traversal node, 32 B = 2 x uint4 (ONE 32-B sector per visit): the two child boxes on a 16-bit grid over the root box,
 //   c[s] = (lo.x | hi.x << 16, lo.y | hi.y << 16, lo.z | hi.z << 16, child index as in BvhNode)
+// A child that is a bottom node over two single triangles k < k' with k' - k <= 15 is folded into this node as the leaf
+// reference ~(k | (k' - k) << 26): the two triangles of a quad have almost the same box, so a ray that enters one nearly
+// always enters the other, and one reference saves the node visit and the second stop of the lane (MCPT_LEAF_BITS = 26).
 // lo rounded down and hi rounded up by two cells, so the quantised box contains the FP32 box with room for the
 // decode's rounding (DESIGN.md "quantised nodes").  Half the loads of BvhNode: traversal is bound by L1 wavefronts.
 struct __align__(16) QNode { uint4 c[2]; };
+#define MCPT_LEAF_BITS 26
 // Grid of the quantisation, 8 floats: origin.xyz, 0, cell.xyz, 0  (world = origin + q * cell)
 struct __align__(16) QGrid { float4 origin, cell; };
 

@@ -172,9 +172,19 @@ __device__ __forceinline__ unsigned quant_hi(float x, float o, float inv_cell) {
     const float q = ceilf((x - o) * inv_cell) + 2.0f;
     return (unsigned)fminf(fmaxf(q, 0.0f), 65535.0f);
 }
+// Child reference of a traversal node: a bottom node over two single triangles becomes one two-triangle leaf reference.
+__device__ __forceinline__ unsigned fold_leaf_pair(const BvhNode* __restrict__ nodes, const int c, const bool fold) {
+    if (c < 0 || !fold) return (unsigned)c;
+    const float4 q3 = nodes[c].q[3];
+    const int a = __float_as_int(q3.x), b = __float_as_int(q3.y);
+    if (a >= 0 || b >= 0) return (unsigned)c;
+    const int ka = ~a, kb = ~b, lo = min(ka, kb), d = max(ka, kb) - lo;
+    if (d == 0 || d > 15 || lo >= (1 << MCPT_LEAF_BITS)) return (unsigned)c;
+    return ~((unsigned)lo | ((unsigned)d << MCPT_LEAF_BITS));
+}
 __global__ void __launch_bounds__(256) quantize_nodes_kernel(int n_nodes, const BvhNode* __restrict__ nodes,
                                                              const float* __restrict__ root_box, QNode* __restrict__ qnodes,
-                                                             QGrid* __restrict__ qgrid) {
+                                                             QGrid* __restrict__ qgrid, const bool fold) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_nodes) return;
     float o[3], cell[3], inv[3];
@@ -194,10 +204,10 @@ __global__ void __launch_bounds__(256) quantize_nodes_kernel(int n_nodes, const 
     QNode out;
     out.c[0] = make_uint4(quant_lo(q0.x, o[0], inv[0]) | (quant_hi(q0.y, o[0], inv[0]) << 16),
                           quant_lo(q0.z, o[1], inv[1]) | (quant_hi(q0.w, o[1], inv[1]) << 16),
-                          quant_lo(q2.x, o[2], inv[2]) | (quant_hi(q2.y, o[2], inv[2]) << 16), __float_as_uint(q3.x));
+                          quant_lo(q2.x, o[2], inv[2]) | (quant_hi(q2.y, o[2], inv[2]) << 16), fold_leaf_pair(nodes, __float_as_int(q3.x), fold));
     out.c[1] = make_uint4(quant_lo(q1.x, o[0], inv[0]) | (quant_hi(q1.y, o[0], inv[0]) << 16),
                           quant_lo(q1.z, o[1], inv[1]) | (quant_hi(q1.w, o[1], inv[1]) << 16),
-                          quant_lo(q2.z, o[2], inv[2]) | (quant_hi(q2.w, o[2], inv[2]) << 16), __float_as_uint(q3.y));
+                          quant_lo(q2.z, o[2], inv[2]) | (quant_hi(q2.w, o[2], inv[2]) << 16), fold_leaf_pair(nodes, __float_as_int(q3.y), fold));
     qnodes[i] = out;
 }
 
@@ -233,7 +243,7 @@ int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches) {
         if (pe) return pe;
         walk = sb.nodes2; sb.root = n - 2;
     }
-    quantize_nodes_kernel<<<(n_nodes + tpb - 1) / tpb, tpb, 0, stream>>>(n_nodes, walk, sb.root_box, sb.qnodes, sb.qgrid); nl++;
+    quantize_nodes_kernel<<<(n_nodes + tpb - 1) / tpb, tpb, 0, stream>>>(n_nodes, walk, sb.root_box, sb.qnodes, sb.qgrid, sb.fold_pairs && n > 2); nl++;
     if (launches) *launches = nl;
     sb.built = true;
     return (int)cudaGetLastError();

@@ -24,6 +24,7 @@ struct SceneBuffers {
     void* cub_temp = nullptr; size_t cub_temp_bytes = 0;
     // quality pass (ploc.cu): the tree traversal walks
     bool use_ploc = true;              // MCPT_BVH=lbvh keeps the radix tree for traversal (A/B measurements)
+    bool fold_pairs = true;            // MCPT_LEAF_PAIRS=0 keeps one triangle per leaf reference (A/B measurements)
     BvhNode* nodes2 = nullptr;         // PLOC tree, n-1 nodes, root = n-2
     float4* cl_lo[2] = {nullptr, nullptr}; float4* cl_hi[2] = {nullptr, nullptr};   // cluster boxes (+ref in lo.w), ping-pong
     int* ploc_nn = nullptr; unsigned long long* ploc_flag = nullptr; unsigned long long* ploc_scan = nullptr;

@@ -114,11 +114,22 @@ __device__ __forceinline__ void tri_test(const TriGeom* __restrict__ tris, const
     }
 }
 
-// One leaf step: test triangle ~node, then pop.
+// Leaf references of the traversal nodes (device_types.cuh QNode): ~(k | delta << 26) = triangle k and, when delta != 0,
+// triangle k + delta (a bottom node whose two children were single triangles, folded into its parent by K4).
+__device__ __forceinline__ int leaf_first(const int ref) { return ~ref & ((1 << MCPT_LEAF_BITS) - 1); }
+__device__ __forceinline__ int leaf_delta(const int ref) { return (~ref >> MCPT_LEAF_BITS) & 15; }
+template <bool COUNT>
+__device__ __forceinline__ void leaf_test(const TriGeom* __restrict__ tris, const int ref, const RayCtx& r, Hit& best, unsigned& n_tris) {
+    const int k = leaf_first(ref), dk = leaf_delta(ref);
+    tri_test<COUNT>(tris, k, r, best, n_tris);
+    if (dk) tri_test<COUNT>(tris, k + dk, r, best, n_tris);
+}
+
+// One leaf step: test the triangle(s) of leaf reference `node`, then pop.
 template <bool COUNT>
 __device__ __forceinline__ void leaf_step(const TriGeom* __restrict__ tris, int& node, const RayCtx& r, Hit& best, int* stack,
                                           int& sp, unsigned& n_tris) {
-    tri_test<COUNT>(tris, ~node, r, best, n_tris);
+    leaf_test<COUNT>(tris, node, r, best, n_tris);
     node = stack[--sp];
 }
 

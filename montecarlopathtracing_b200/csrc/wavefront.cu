@@ -340,7 +340,7 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
         const unsigned nm = __ballot_sync(0xffffffffu, node >= 0);
         if (COUNT && lane == 0) { w_iter++; if (pm != 0u && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) w_tri++; }
         if (has_p && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) {
-            tri_test<COUNT>(sc.tri, ~pend, r, best, n_tris);
+            leaf_test<COUNT>(sc.tri, pend, r, best, n_tris);
 #if MCPT_PEND2
             pend = pend2; pend2 = 0;
 #else
