@@ -23,7 +23,7 @@ NVCC_FLAGS = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-ccbin", CXX, "-Xcompile
 NVCC_FLAGS += os.environ.get("MCPT_NVCC_EXTRA", "").split()   # developer knob for A/B builds (e.g. -DMCPT_SHADE_MIN_CTAS=5)
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall"]
 
-CU_SOURCES = {"lbvh.cu": ["--fmad=false"], "ploc.cu": [], "render.cu": [], "wavefront.cu": [], "png_device.cu": [], "obj_ingest.cu": [], "api.cu": []}
+CU_SOURCES = {"lbvh.cu": ["--fmad=false"], "ploc.cu": [], "wide.cu": [], "render.cu": [], "wavefront.cu": [], "png_device.cu": [], "obj_ingest.cu": [], "api.cu": []}
 CPP_SOURCES = ["scene_loader.cpp", "png_writer.cpp", "render_scene.cpp", "mcpt_error.cpp"]
 
 

@@ -90,7 +90,7 @@ double face_area(const double* p) {
 DeviceScene device_scene(const mcpt_ctx* c) {
     DeviceScene d{};
     d.n_faces = c->sb.n_faces; d.n_materials = c->n_materials; d.n_textures = c->n_textures; d.n_lights = c->n_lights;
-    d.root = c->sb.root; d.area0 = c->area0;
+    d.root = MCPT_WIDE ? 0 : c->sb.root; d.qnodes4 = c->sb.qnodes4; d.area0 = c->area0;
     d.nodes = c->sb.nodes; d.qnodes = c->sb.qnodes; d.qgrid = c->sb.qgrid; d.tri = c->sb.tri; d.shade = c->sb.shade; d.leaf_face = c->sb.leaf_face; d.pos = c->sb.pos;
     d.materials = c->d_materials; d.textures = c->d_textures; d.tex_bytes = c->d_tex_bytes;
     d.lights = c->d_lights; d.light_tris = c->d_light_tris; d.light_cdf = c->d_light_cdf;
@@ -136,6 +136,7 @@ int alloc_scene(mcpt_ctx* c, int n) {
         carve(s.codes_obj, N); carve(s.codes_sorted, N); carve(s.iota, N); carve(s.leaf_face, N);
         carve(s.leaf_parent, N); carve(s.flags, N); carve(s.nodes, N); carve(s.tri, N);
         carve(s.shade, N); carve(s.root_box, 6); carve(s.qnodes, N); carve(s.qgrid, 1);
+        carve(s.qnodes4, N); carve(s.w4_queue, N); carve(s.w4_ctr, 4);
         carve(s.nodes2, N); carve(s.cl_lo[0], N); carve(s.cl_lo[1], N); carve(s.cl_hi[0], N); carve(s.cl_hi[1], N);
         carve(s.ploc_nn, N); carve(s.ploc_flag, N); carve(s.ploc_scan, N);
         carve_bytes(s.ploc_temp, s.ploc_temp_bytes); carve_bytes(s.ploc_state, 64); carve_bytes(s.cub_temp, s.cub_temp_bytes);
@@ -498,6 +499,11 @@ MCPT_API int mcpt_build_bvh(mcpt_ctx* c, float* ms_out) {
     CU(cudaEventSynchronize(c->ev1));
     CU(cudaEventElapsedTime(&c->last_build_ms, c->ev0, c->ev1));
     if (ms_out) *ms_out = c->last_build_ms;
+#if MCPT_WIDE
+    unsigned w4[4] = {0, 0, 0, 0};
+    CU(cudaMemcpy(w4, c->sb.w4_ctr, sizeof(w4), cudaMemcpyDeviceToHost));
+    if (w4[3] || !w4[2]) return fail_cuda(cudaErrorLaunchTimeout, "wide_build: the breadth-first collapse did not finish");
+#endif
     return MCPT_OK;
 }
 

@@ -23,6 +23,13 @@ struct __align__(16) BvhNode { float4 q[4]; };
 // decode's rounding (DESIGN.md "quantised nodes").  Half the loads of BvhNode: traversal is bound by L1 wavefronts.
 struct __align__(16) QNode { uint4 c[2]; };
 #define MCPT_LEAF_BITS 26
+// 4-wide traversal node, 64 B = 4 x uint4, same per-child encoding as QNode; an unused slot holds an inverted box (never
+// hit).  Built from the binary tree by K4b (wide.cu), breadth-first, root = node 0.  MCPT_WIDE selects which tree the
+// traversal kernels walk (compile time: the node step is the innermost loop).
+struct __align__(16) QNode4 { uint4 c[4]; };
+#ifndef MCPT_WIDE
+#define MCPT_WIDE 1
+#endif
 // Grid of the quantisation, 8 floats: origin.xyz, 0, cell.xyz, 0  (world = origin + q * cell)
 struct __align__(16) QGrid { float4 origin, cell; };
 
@@ -60,6 +67,7 @@ struct DeviceScene {
     float area0;              // area of light 0: the frozen range of the selection uniform (quirk Q6)
     const BvhNode* nodes;     // FP32 nodes (build product, structural tests)
     const QNode* qnodes;      // 16-bit quantised nodes (what traversal reads)
+    const QNode4* qnodes4;    // 4-wide quantised nodes (MCPT_WIDE)
     const QGrid* qgrid;
     const TriGeom* tri;
     const TriShade* shade;

@@ -5,6 +5,7 @@
 // must be IEEE-identical to the host's.
 #include <cub/device/device_radix_sort.cuh>
 #include "lbvh.h"
+#include "quant.cuh"
 
 namespace mcpt {
 
@@ -161,41 +162,14 @@ __global__ void __launch_bounds__(256) emit_refit_kernel(int n, const double* __
 }
 
 // ---- K4: quantise the refitted nodes onto a 16-bit grid over the root box ----------------------------------
-// One thread per internal node: 64-B FP32 node in, 32-B node out.  lo is floored and hi is ceiled, then both are
-// pushed out by two more cells: one for the float rounding of (x - origin) / cell here, one for the half-cell error of
-// the magic-number decode in node_step (trace.cuh).
-__device__ __forceinline__ unsigned quant_lo(float x, float o, float inv_cell) {
-    const float q = floorf((x - o) * inv_cell) - 2.0f;
-    return (unsigned)fminf(fmaxf(q, 0.0f), 65535.0f);
-}
-__device__ __forceinline__ unsigned quant_hi(float x, float o, float inv_cell) {
-    const float q = ceilf((x - o) * inv_cell) + 2.0f;
-    return (unsigned)fminf(fmaxf(q, 0.0f), 65535.0f);
-}
-// Child reference of a traversal node: a bottom node over two single triangles becomes one two-triangle leaf reference.
-__device__ __forceinline__ unsigned fold_leaf_pair(const BvhNode* __restrict__ nodes, const int c, const bool fold) {
-    if (c < 0 || !fold) return (unsigned)c;
-    const float4 q3 = nodes[c].q[3];
-    const int a = __float_as_int(q3.x), b = __float_as_int(q3.y);
-    if (a >= 0 || b >= 0) return (unsigned)c;
-    const int ka = ~a, kb = ~b, lo = min(ka, kb), d = max(ka, kb) - lo;
-    if (d == 0 || d > 15 || lo >= (1 << MCPT_LEAF_BITS)) return (unsigned)c;
-    return ~((unsigned)lo | ((unsigned)d << MCPT_LEAF_BITS));
-}
+// One thread per internal node: 64-B FP32 node in, 32-B node out (grid and rounding rules: quant.cuh).
 __global__ void __launch_bounds__(256) quantize_nodes_kernel(int n_nodes, const BvhNode* __restrict__ nodes,
                                                              const float* __restrict__ root_box, QNode* __restrict__ qnodes,
                                                              QGrid* __restrict__ qgrid, const bool fold) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_nodes) return;
     float o[3], cell[3], inv[3];
-#pragma unroll
-    for (int a = 0; a < 3; a++) {
-        const float lo = root_box[a], hi = root_box[3 + a];
-        const float ext = fmaxf(hi - lo, 1.0e-20f);
-        cell[a] = ext * (1.0f / 65520.0f);            // the root box spans cells 8 .. 65528: room for the outward push
-        o[a] = lo - 8.0f * cell[a];
-        inv[a] = 1.0f / cell[a];
-    }
+    quant_grid(root_box, o, cell, inv);
     if (i == 0) {
         qgrid->origin = make_float4(o[0], o[1], o[2], 0.0f);
         qgrid->cell = make_float4(cell[0], cell[1], cell[2], 0.0f);
@@ -204,10 +178,10 @@ __global__ void __launch_bounds__(256) quantize_nodes_kernel(int n_nodes, const 
     QNode out;
     out.c[0] = make_uint4(quant_lo(q0.x, o[0], inv[0]) | (quant_hi(q0.y, o[0], inv[0]) << 16),
                           quant_lo(q0.z, o[1], inv[1]) | (quant_hi(q0.w, o[1], inv[1]) << 16),
-                          quant_lo(q2.x, o[2], inv[2]) | (quant_hi(q2.y, o[2], inv[2]) << 16), fold_leaf_pair(nodes, __float_as_int(q3.x), fold));
+                          quant_lo(q2.x, o[2], inv[2]) | (quant_hi(q2.y, o[2], inv[2]) << 16), (unsigned)fold_leaf_pair(nodes, __float_as_int(q3.x), fold));
     out.c[1] = make_uint4(quant_lo(q1.x, o[0], inv[0]) | (quant_hi(q1.y, o[0], inv[0]) << 16),
                           quant_lo(q1.z, o[1], inv[1]) | (quant_hi(q1.w, o[1], inv[1]) << 16),
-                          quant_lo(q2.z, o[2], inv[2]) | (quant_hi(q2.w, o[2], inv[2]) << 16), fold_leaf_pair(nodes, __float_as_int(q3.y), fold));
+                          quant_lo(q2.z, o[2], inv[2]) | (quant_hi(q2.w, o[2], inv[2]) << 16), (unsigned)fold_leaf_pair(nodes, __float_as_int(q3.y), fold));
     qnodes[i] = out;
 }
 
@@ -244,6 +218,9 @@ int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches) {
         walk = sb.nodes2; sb.root = n - 2;
     }
     quantize_nodes_kernel<<<(n_nodes + tpb - 1) / tpb, tpb, 0, stream>>>(n_nodes, walk, sb.root_box, sb.qnodes, sb.qgrid, sb.fold_pairs && n > 2); nl++;
+#if MCPT_WIDE
+    { const int we = wide_build(sb, walk, sb.root, stream, &nl); if (we) return we; }
+#endif
     if (launches) *launches = nl;
     sb.built = true;
     return (int)cudaGetLastError();

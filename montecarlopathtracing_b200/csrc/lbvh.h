@@ -21,6 +21,9 @@ struct SceneBuffers {
     float* root_box = nullptr;         // 6 floats: lo.xyz, hi.xyz
     QNode* qnodes = nullptr;           // traversal nodes, same indexing as `nodes`
     QGrid* qgrid = nullptr;
+    QNode4* qnodes4 = nullptr;         // 4-wide traversal nodes (wide.cu), breadth-first, root = 0
+    int* w4_queue = nullptr;           // wide node -> the binary node it is rooted at
+    unsigned* w4_ctr = nullptr;        // queue tail (= number of wide nodes), processed, finished, error
     void* cub_temp = nullptr; size_t cub_temp_bytes = 0;
     // quality pass (ploc.cu): the tree traversal walks
     bool use_ploc = true;              // MCPT_BVH=lbvh keeps the radix tree for traversal (A/B measurements)
@@ -42,5 +45,8 @@ int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches);
 // K4a (ploc.cu): parallel locally-ordered clustering over the Morton-ordered leaf boxes -> sb.nodes2.
 size_t ploc_scan_temp_bytes(int n);
 int ploc_build(SceneBuffers& sb, cudaStream_t stream, int* launches);
+
+// K4b (wide.cu): collapse the binary traversal tree `walk` (root `root2`) into sb.qnodes4.
+int wide_build(SceneBuffers& sb, const BvhNode* walk, int root2, cudaStream_t stream, int* launches);
 
 }  // namespace mcpt

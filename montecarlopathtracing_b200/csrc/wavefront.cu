@@ -257,7 +257,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
 #define MCPT_PEND2 0
 #endif
 #ifndef MCPT_TRACE_MIN_CTAS
-#define MCPT_TRACE_MIN_CTAS 8
+#define MCPT_TRACE_MIN_CTAS 9
 #endif
 template <bool COUNT>
 __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const DeviceScene sc, const WfBuffers B, const int iter, unsigned long long* stats,
@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[0], (unsigned long long)n);
     RayCtx r = ray_setup(f3(0.f, 0.f, 0.f), f3(1.f, 1.f, 1.f), sc.qgrid);
     Hit best; best.t = 0.f; best.u = 0.f; best.v = 0.f; best.k = -1;
-    int stack[MCPT_STACK_SIZE];
+    int stack[MCPT_STACK_SIZE + 4];
     stack[0] = MCPT_SENT;
     int sp = 1, node = MCPT_SENT;
     unsigned id = 0;
@@ -326,7 +326,11 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
                 const unsigned fin_m = __ballot_sync(0xffffffffu, node == MCPT_SENT && pend != 0);
                 if (at_node != 0u && lane == 0) { w_node++; w_idle += __popc(idle_m); w_fin += __popc(fin_m); }
             }
+#if MCPT_WIDE
+            if (node >= 0) node4_step<COUNT>(sc.qnodes4, node, r, best.t, stack, sp, n_nodes);
+#else
             if (node >= 0) node_step<COUNT>(sc.qnodes, node, r, best.t, stack, sp, n_nodes);
+#endif
             if (node < 0 && node != MCPT_SENT) {
                 if (pend == 0) { pend = node; node = stack[--sp]; }
 #if MCPT_PEND2
@@ -439,7 +443,7 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
     const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
     const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 16) / pipes;   // CTAs of 4 warps, shared by the pipes
     const int refill_min = env_int("MCPT_REFILL_MIN", 12), leaf_min = env_int("MCPT_LEAF_MIN", 12),
-              block_min = env_int("MCPT_BLOCK_MIN", 4), node_steps = env_int("MCPT_NODE_STEPS", 4);
+              block_min = env_int("MCPT_BLOCK_MIN", 4), node_steps = env_int("MCPT_NODE_STEPS", MCPT_WIDE ? 2 : 4);
     const int batch = 8;
     const bool diag = getenv("MCPT_DIAG_ALIVE") != nullptr;
     int nlaunch = 0, n_timed = 0;

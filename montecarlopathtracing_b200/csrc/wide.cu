@@ -1,0 +1,110 @@
+// wide.cu — K4b: collapse the binary traversal tree into a 4-wide tree of 64-B quantised nodes (QNode4).
+//
+// Why: wf_trace is bound by the latency of one dependent node fetch per step with ~36 resident warps per SM (ncu: issue
+// slots half empty, long-scoreboard the top stall).  A 4-wide node halves the number of dependent steps per ray and gives
+// every step four independent slab tests, and the node array shrinks from (n-1) x 32 B to ~(n/2.4) x 64 B.
+//
+// How: breadth-first, ONE launch.  Thread t owns wide node t: it waits until queue[t] names the binary node the wide node
+// is rooted at, opens that node's two children, then twice more the open child with the largest surface area (up to four
+// children; a bottom node over two single triangles counts as a leaf, see fold_leaf_pair), reserves consecutive wide-node
+// indices for its internal children with one atomicAdd on the queue tail and writes their binary roots into the queue.
+// Producers always have a lower index than their consumers and CTAs are dispatched in index order, so every waiting thread's
+// producer is resident or finished; a warp polls with all its lanes in step (no lane spins while a lane of the same warp
+// that it depends on is held back), and the wait is bounded (error flag instead of a hang).
+// The layout is breadth-first, so the top of the tree is contiguous; which sibling subtree gets the lower index depends on
+// the order of the atomics, the TREE (and therefore every traversal result) does not.
+#include "lbvh.h"
+#include "quant.cuh"
+
+namespace mcpt {
+
+enum { W4_TAIL = 0, W4_PROCESSED = 1, W4_FINISHED = 2, W4_ERROR = 3 };
+#define W4_EMPTY (-1)
+#define W4_SPIN_LIMIT (1 << 20)
+
+struct W4Slot { float lo[3], hi[3]; int ref; };
+
+__device__ __forceinline__ void w4_children(const BvhNode* __restrict__ nodes, const int id, const bool fold, W4Slot& a, W4Slot& b) {
+    const float4 q0 = nodes[id].q[0], q1 = nodes[id].q[1], q2 = nodes[id].q[2], q3 = nodes[id].q[3];
+    a.lo[0] = q0.x; a.hi[0] = q0.y; a.lo[1] = q0.z; a.hi[1] = q0.w; a.lo[2] = q2.x; a.hi[2] = q2.y;
+    b.lo[0] = q1.x; b.hi[0] = q1.y; b.lo[1] = q1.z; b.hi[1] = q1.w; b.lo[2] = q2.z; b.hi[2] = q2.w;
+    a.ref = fold_leaf_pair(nodes, __float_as_int(q3.x), fold);
+    b.ref = fold_leaf_pair(nodes, __float_as_int(q3.y), fold);
+}
+__device__ __forceinline__ float w4_area(const W4Slot& s) {
+    const float dx = s.hi[0] - s.lo[0], dy = s.hi[1] - s.lo[1], dz = s.hi[2] - s.lo[2];
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void __launch_bounds__(256) wide_init_kernel(unsigned* ctr) {
+    ctr[W4_TAIL] = 1u; ctr[W4_PROCESSED] = 0u; ctr[W4_FINISHED] = 0u; ctr[W4_ERROR] = 0u;
+}
+
+__global__ void __launch_bounds__(256) wide_collapse_kernel(const BvhNode* __restrict__ nodes, const int root2, const int max_nodes,
+                                                            const float* __restrict__ root_box, QNode4* __restrict__ out,
+                                                            int* queue, unsigned* ctr, const bool fold) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    bool done = t >= max_nodes;
+    for (int spin = 0;; spin++) {
+        if (!done) {
+            const int id = t == 0 ? root2 : *(volatile int*)&queue[t];
+            if (id != W4_EMPTY) {
+                W4Slot s[4];
+                int cnt = 2;
+                w4_children(nodes, id, fold, s[0], s[1]);
+                for (int step = 0; step < 2; step++) {
+                    int pick = -1; float best = -1.0f;
+                    for (int j = 0; j < cnt; j++) {
+                        const float a = w4_area(s[j]);
+                        if (s[j].ref >= 0 && a > best) { best = a; pick = j; }
+                    }
+                    if (pick < 0) break;
+                    const int open = s[pick].ref;
+                    w4_children(nodes, open, fold, s[pick], s[cnt]);
+                    cnt++;
+                }
+                int m = 0;
+                for (int j = 0; j < cnt; j++) m += s[j].ref >= 0;
+                unsigned base = 0;
+                if (m) base = atomicAdd(&ctr[W4_TAIL], (unsigned)m);
+                float o[3], cell[3], inv[3];
+                quant_grid(root_box, o, cell, inv);
+                QNode4 q;
+                int k = 0;
+                for (int j = 0; j < 4; j++) {
+                    if (j < cnt) {
+                        int ref = s[j].ref;
+                        if (ref >= 0) { const int w = (int)base + k++; *(volatile int*)&queue[w] = ref; ref = w; }
+                        q.c[j] = make_uint4(quant_lo(s[j].lo[0], o[0], inv[0]) | (quant_hi(s[j].hi[0], o[0], inv[0]) << 16),
+                                            quant_lo(s[j].lo[1], o[1], inv[1]) | (quant_hi(s[j].hi[1], o[1], inv[1]) << 16),
+                                            quant_lo(s[j].lo[2], o[2], inv[2]) | (quant_hi(s[j].hi[2], o[2], inv[2]) << 16), (unsigned)ref);
+                    } else {
+                        q.c[j] = make_uint4(0x0000FFFFu, 0x0000FFFFu, 0x0000FFFFu, 0x80000000u);   // inverted box: never hit
+                    }
+                }
+                out[t] = q;
+                __threadfence();
+                const unsigned p = atomicAdd(&ctr[W4_PROCESSED], 1u) + 1u;
+                if (p == atomicAdd(&ctr[W4_TAIL], 0u)) *(volatile unsigned*)&ctr[W4_FINISHED] = 1u;
+                done = true;
+            }
+        }
+        const bool fin = *(volatile unsigned*)&ctr[W4_FINISHED] != 0u;
+        if (__all_sync(0xffffffffu, done || fin)) break;
+        if (spin > W4_SPIN_LIMIT) { ctr[W4_ERROR] = 1u; *(volatile unsigned*)&ctr[W4_FINISHED] = 1u; break; }   // releases every other waiter too
+    }
+}
+
+int wide_build(SceneBuffers& sb, const BvhNode* walk, int root2, cudaStream_t stream, int* launches) {
+    const int n = sb.n_faces;
+    const int max_nodes = n > 1 ? n - 1 : 1;
+    cudaError_t e = cudaMemsetAsync(sb.w4_queue, 0xFF, sizeof(int) * (size_t)max_nodes, stream);
+    if (e != cudaSuccess) return (int)e;
+    wide_init_kernel<<<1, 1, 0, stream>>>(sb.w4_ctr);
+    wide_collapse_kernel<<<(max_nodes + 255) / 256, 256, 0, stream>>>(walk, root2, max_nodes, sb.root_box, sb.qnodes4, sb.w4_queue,
+                                                                      sb.w4_ctr, sb.fold_pairs && n > 2);
+    if (launches) *launches += 3;
+    return (int)cudaGetLastError();
+}
+
+}  // namespace mcpt
