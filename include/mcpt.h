@@ -185,6 +185,12 @@ MCPT_API int mcpt_get_nodes(mcpt_ctx* ctx, float* nodes16, int32_t* root);
 /* The tree traversal walks: the radix tree's leaves re-clustered by surface area (PLOC), same node format
  * and leaf indices; root is n_faces-2.  With MCPT_BVH=lbvh in the environment it is the radix tree itself. */
 MCPT_API int mcpt_get_traversal_tree(mcpt_ctx* ctx, float* nodes16, int32_t* root);
+/* The 4-wide tree the traversal kernels read: the tree above collapsed breadth-first, root = node 0.
+ * nodes16 (may be NULL): capacity max(n_faces-1,1) nodes x 16 uint32 = 4 children x (lo.x | hi.x << 16, lo.y | hi.y << 16,
+ * lo.z | hi.z << 16, ref) on the 16-bit grid grid8 = (origin.xyz, 0, cell.xyz, 0): world = origin + q * cell.
+ * ref >= 0: wide node; ref < 0: leaf ~(k | d << 26) = sorted triangle k and, when d != 0, k + d; an unused slot has an
+ * inverted box (lo = 0xFFFF, hi = 0).  n_wide = number of nodes in use (they are nodes 0 .. n_wide-1). */
+MCPT_API int mcpt_get_wide_tree(mcpt_ctx* ctx, uint32_t* nodes16, int32_t* n_wide, float* grid8);
 
 /* Seam 2. Closest hit of n rays, HOST buffers: org_dir = n x 6 floats (origin, direction; the
  * direction need not be unit).  Tie rule and the d.x==0 quirk follow MTPC/pathTracing.cpp:347-361. */

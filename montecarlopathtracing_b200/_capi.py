@@ -72,6 +72,7 @@ SIGNATURES = {
     "mcpt_get_morton": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "mcpt_get_nodes": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32)]),
     "mcpt_get_traversal_tree": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32)]),
+    "mcpt_get_wide_tree": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_void_p]),
     "mcpt_trace": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(Stats)]),
     "mcpt_trace_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(Stats)]),
     "mcpt_render": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,

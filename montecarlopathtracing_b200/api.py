@@ -171,6 +171,15 @@ class Context:
         check(lib().mcpt_get_traversal_tree(self._c, nodes.ctypes.data, C.byref(root)))
         return nodes, root.value
 
+    def get_wide_tree(self):
+        """(nodes (n_wide, 4, 4) uint32, grid origin (3,), grid cell (3,)) of the 4-wide traversal tree."""
+        cap = max(self.n_faces - 1, 1)
+        nodes = np.empty((cap, 4, 4), np.uint32)
+        n_wide = C.c_int32()
+        grid = np.empty(8, np.float32)
+        check(lib().mcpt_get_wide_tree(self._c, nodes.ctypes.data, C.byref(n_wide), grid.ctypes.data))
+        return nodes[:n_wide.value].copy(), grid[0:3].copy(), grid[4:7].copy()
+
     def trace(self, org_dir):
         """org_dir: (n,6) float32 host array -> structured array of hits (t,u,v,tri,leaf)."""
         rays = np.ascontiguousarray(org_dir, dtype=np.float32).reshape(-1, 6)

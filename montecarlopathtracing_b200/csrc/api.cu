@@ -528,6 +528,19 @@ MCPT_API int mcpt_get_nodes(mcpt_ctx* c, float* nodes16, int32_t* root) {
     return MCPT_OK;
 }
 
+MCPT_API int mcpt_get_wide_tree(mcpt_ctx* c, uint32_t* nodes16, int32_t* n_wide, float* grid8) {
+    if (!c || !c->sb.built) return fail_arg("mcpt_get_wide_tree: build the BVH first");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    unsigned w4[4] = {0, 0, 0, 0};
+    CU(cudaMemcpy(w4, c->sb.w4_ctr, sizeof(w4), cudaMemcpyDeviceToHost));
+    if (n_wide) *n_wide = (int32_t)w4[0];
+    const int cap = c->sb.n_faces > 1 ? c->sb.n_faces - 1 : 1;
+    if (nodes16) CU(cudaMemcpy(nodes16, c->sb.qnodes4, sizeof(QNode4) * (size_t)cap, cudaMemcpyDeviceToHost));
+    if (grid8) CU(cudaMemcpy(grid8, c->sb.qgrid, sizeof(QGrid), cudaMemcpyDeviceToHost));
+    return MCPT_OK;
+}
+
 MCPT_API int mcpt_get_traversal_tree(mcpt_ctx* c, float* nodes16, int32_t* root) {
     if (!c || !c->sb.built) return fail_arg("mcpt_get_traversal_tree: build the BVH first");
     CU(cudaSetDevice(c->device));

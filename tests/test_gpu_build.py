@@ -175,3 +175,80 @@ def test_traversal_tree_small_counts(gpu_ctx, n):
     nodes, root = gpu_ctx.get_traversal_tree()
     p = keep[0].reshape(n, 3, 3)[face_sorted].astype(np.float32).astype(np.float64)
     check_traversal_tree(nodes, root, n, p.min(axis=1), p.max(axis=1))
+
+
+def check_wide_tree(nodes, origin, cell, n, tri_lo, tri_hi, binary_nodes=None):
+    """The 4-wide tree the kernels walk (wide.cu): node 0 is the root, every node 0..n_wide-1 is referenced exactly once, every
+    sorted triangle sits in exactly one leaf reference, every child's dequantised box contains its subtree, unused slots
+    can never be hit, and a leaf pair is at most 15 apart."""
+    n_wide = len(nodes)
+    q = nodes[:, :, :3]
+    lo = origin + (q & 0xFFFF).astype(np.float64) * cell          # (n_wide, 4, 3)
+    hi = origin + (q >> 16).astype(np.float64) * cell
+    ref = nodes[:, :, 3].view(np.int32)
+    unused = np.all((q & 0xFFFF) == 0xFFFF, axis=2) & np.all((q >> 16) == 0, axis=2)
+    assert np.all(ref[unused] == np.int32(-2**31))
+    assert np.all(np.sum(~unused, axis=1) >= 2), "a wide node has at least two children"
+    inner = (ref >= 0) & ~unused
+    leaf = (ref < 0) & ~unused
+    # internal references: a permutation of 1..n_wide-1
+    assert np.array_equal(np.sort(ref[inner]), np.arange(1, n_wide))
+    # leaves: every triangle exactly once
+    bits = ~ref[leaf]
+    k0, d = bits & ((1 << 26) - 1), (bits >> 26) & 15
+    assert np.all((bits >> 30) == 0)
+    tris = np.concatenate([k0, (k0 + d)[d > 0]])
+    if n > 1:
+        assert np.array_equal(np.sort(tris), np.arange(n)), "triangles are not covered exactly once"
+    # leaf boxes contain their triangles (on the grid, pushed outward)
+    llo, lhi = lo[leaf], hi[leaf]
+    assert np.all(llo <= tri_lo[k0]) and np.all(lhi >= tri_hi[k0])
+    assert np.all(llo[d > 0] <= tri_lo[(k0 + d)[d > 0]]) and np.all(lhi[d > 0] >= tri_hi[(k0 + d)[d > 0]])
+    # a child box contains the boxes of that child's children; breadth-first numbering => children have larger indices
+    pi, ps = np.nonzero(inner)
+    ci = ref[pi, ps]
+    assert np.all(ci > pi)
+    used = ~unused[ci]                                            # (m, 4)
+    clo = np.where(used[:, :, None], lo[ci], np.inf).min(axis=1)
+    chi = np.where(used[:, :, None], hi[ci], -np.inf).max(axis=1)
+    assert np.all(lo[pi, ps] <= clo + 1e-9) and np.all(hi[pi, ps] >= chi - 1e-9)
+    # grid boxes are tight: at most 3 cells (+ float rounding) beyond the FP32 leaf box
+    slack = 3.5 * cell + 1e-6 * (1 + np.abs(tri_lo[k0]))
+    single = d == 0
+    assert np.all(llo[single] >= tri_lo[k0][single] - slack[single]) and np.all(lhi[single] <= tri_hi[k0][single] + slack[single])
+    return n_wide
+
+
+@pytest.mark.parametrize("name", SCENE_NAMES)
+def test_wide_tree_invariants_on_shipped_scenes(gpu_ctx, scenes, name):
+    s = scenes[name]
+    gpu_ctx.upload_scene(s)
+    gpu_ctx.build_bvh()
+    _, _, face_sorted = gpu_ctx.get_morton()
+    nodes, origin, cell = gpu_ctx.get_wide_tree()
+    p = s.pos[face_sorted].astype(np.float32).astype(np.float64)
+    n_wide = check_wide_tree(nodes, origin.astype(np.float64), cell.astype(np.float64), s.n_faces, p.min(axis=1), p.max(axis=1))
+    assert n_wide < 0.55 * s.n_faces, "the collapse should leave well under n/2 nodes"
+    # a rebuild gives the same TREE (numbering inside a level may differ: it comes from atomics): same multiset of leaf sets
+    gpu_ctx.build_bvh()
+    nodes2, _, _ = gpu_ctx.get_wide_tree()
+    assert len(nodes2) == n_wide
+    def leaf_sets(nd):
+        r = nd[:, :, 3].view(np.int32)
+        return sorted(tuple(sorted(int(x) for x in row if x < 0 and x != -2**31)) for row in r)
+    assert leaf_sets(nodes) == leaf_sets(nodes2)
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 7, 64, 1001, 1025, 5000])
+def test_wide_tree_small_counts(gpu_ctx, n):
+    desc, keep = random_soup(n, seed=n, far_outside=(n == 64))
+    gpu_ctx.upload_scene(desc)
+    gpu_ctx.build_bvh()
+    _, _, face_sorted = gpu_ctx.get_morton()
+    nodes, origin, cell = gpu_ctx.get_wide_tree()
+    p = keep[0].reshape(n, 3, 3)[face_sorted].astype(np.float32).astype(np.float64)
+    if n == 1:   # degenerate: the root names the only triangle twice
+        r = nodes[0, :, 3].view(np.int32)
+        assert len(nodes) == 1 and r[0] == ~0 and r[1] == ~0
+        return
+    check_wide_tree(nodes, origin.astype(np.float64), cell.astype(np.float64), n, p.min(axis=1), p.max(axis=1))
