@@ -31,7 +31,7 @@ WORKLOADS = {
 # DRAM bytes of ONE launch of the dominant kernel from the committed `ncu --set full` capture (bytes; per launch like
 # roofline.achieved).  ~89 MB (ray queue in, hit records out) against ~1.4 GB of algorithmic node+triangle bytes per launch: the
 # scene is served from L1/L2.
-NCU_TRAFFIC = {("cornell-box-1024x1024-spp256", "wavefront"): 79.893504e6 + 9.083136e6,
+NCU_TRAFFIC = {("cornell-box-1024x1024-spp256", "wavefront"): 79.520256e6 + 10.336000e6,
                ("cornell-box-1024x1024-spp256", "megakernel"): 6.414592e6 + 64.855552e6}
 SYNTHETIC_TRIS = {"synthetic-5M": 5_000_000, "synthetic-1M": 1_000_000}
 DEFAULT_WORKLOAD = "cornell-box-1024x1024-spp256"
@@ -62,6 +62,10 @@ class ClockSampler:
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.p = None
+
+    def mark(self):
+        """Rows read so far belong to the warm-up: drop them (keep the last one so a very short timed region still has a sample)."""
+        self.rows = self.rows[-1:]
 
     def _read(self):
         for line in self.p.stdout:
@@ -242,13 +246,13 @@ def run_ours(args):
         if img is not None:
             host_img.copy_(img, non_blocking=False)
 
-    launches_per_step = None
-    for _ in range(args.warmup):
-        step()
-    barrier()
     sampler = ClockSampler(local)
     if rank == 0:
-        sampler.start()
+        sampler.start()                                      # nvidia-smi takes ~0.3 s to print its first row: start it early,
+    for _ in range(args.warmup):                             # keep only the rows of the timed region (mark() below)
+        step()
+    barrier()
+    sampler.mark()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     integ_ms, render_ms, build_ms, rays, trace_ms, trace_n, launches = [], [], [], [], [], [], 0
     ev0.record(stream)
@@ -258,7 +262,7 @@ def run_ours(args):
         st = stats[-1]
         integ_ms.append(st.integrate_ms); render_ms.append(st.render_ms); build_ms.append(st.build_ms); rays.append(st.rays)
         trace_ms.append(st.trace_ms); trace_n.append(st.trace_launches)
-        launches += 7 + st.kernel_launches + 1     # build (3 ours + 4 CUB) + render_chunks' kernels + the final fixed-tree sum
+        launches += st.build_launches + st.kernel_launches + 1     # build (ours + CUB's) + render_chunks' kernels + the final fixed-tree sum
     ev1.record(stream)
     barrier()
     ms_total = ev0.elapsed_time(ev1)
@@ -283,12 +287,12 @@ def run_ours(args):
         pk, pk_src = peaks()
         samples = float(w) * h * spp * args.steps
         ms_step = ms_total / args.steps
-        # algorithmic bytes of the dominant kernel: 32 B per node fetch + 48 B per triangle test, counted
+        # algorithmic bytes of the dominant kernel: 64 B per 4-wide node fetch + 48 B per triangle test, counted
         # by the COUNT variant on the same workload at reduced spp (per-ray averages are spp-independent)
         cspp = max(8, min(spp_per_gpu, 16))
         ctx.render(camera, cspp, w, h, mode=mode, flags=M.FLAG_COUNT)
         cs = ctx.last_stats
-        bytes_per_ray = (32.0 * cs.node_visits + 48.0 * cs.tri_tests) / cs.rays
+        bytes_per_ray = (64.0 * cs.node_visits + 48.0 * cs.tri_tests) / cs.rays
         # dominant kernel: the megakernel (one launch per step), or wf_trace (one launch per wavefront iteration; its
         # launches of a step are timed by one CUDA-event pair each and summed)
         if args.mode == "wavefront":
@@ -309,26 +313,29 @@ def run_ours(args):
                        "spp_per_gpu": spp_per_gpu, "mode": args.mode, "partition": "spp-split, 64 chunks, fixed-tree sum",
                        "l2_policy": "no flush: the scene (%.1f MB of nodes+triangles) is L1/L2-resident by design and every "
                                     "launch re-reads it millions of times; the wavefront state and ray queues (~%d MB) "
-                                    "exceed L2 at this size" % ((32 + 48 + 64) * n_faces / 1e6, int(w * h * (100 + 16 * n_lights + 32 * (n_lights + 1)) / 1e6))},
+                                    "exceed L2 at this size" % ((0.45 * 64 + 48 + 64) * n_faces / 1e6, int(w * h * (100 + 16 * n_lights + 32 * (n_lights + 1)) / 1e6))},
             "mrays_per_s": rays_total / ms_total * 1e-3, "rays_per_sample": rays_total / samples,
             "lbvh_build_ms": sum(build_ms) / len(build_ms), "render_ms": sum(render_ms) / len(render_ms),
-            # seam 1: 528 algorithmic bytes per triangle over the nine build launches against the HBM peak
-            "lbvh_build_roofline": {"bound": "hbm", "achieved": 528.0 * n_faces / (sum(build_ms) / len(build_ms) * 1e-3) / 1e9,
+            # seam 1: 640 algorithmic bytes per triangle over the radix-tree pipeline + the 4-wide collapse against the HBM peak
+            "lbvh_build_roofline": {"bound": "hbm", "achieved": 640.0 * n_faces / (sum(build_ms) / len(build_ms) * 1e-3) / 1e9,
                                     "peak": pk["hbm_gbs"], "unit": "GB/s",
-                                    "frac": 528.0 * n_faces / (sum(build_ms) / len(build_ms) * 1e-3) / 1e9 / pk["hbm_gbs"]},
+                                    "frac": 640.0 * n_faces / (sum(build_ms) / len(build_ms) * 1e-3) / 1e9 / pk["hbm_gbs"]},
             "e2e": {"value": samples / e2e_ms * 1e-3, "unit": "Msamples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": h * w * 3 * 4, "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
-                         "traffic": NCU_TRAFFIC.get((args.workload, args.mode)), "traffic_source": "profiles/r1_final_wf_trace_ncu.md "
+                         "traffic": NCU_TRAFFIC.get((args.workload, args.mode)), "traffic_source": "profiles/r1_wide_wf_trace_ncu.md "
                          "(dram__bytes_read.sum + dram__bytes_write.sum of one mid-render wf_trace launch; null for workloads not captured)",
                          "peak_source": pk_src, "kernel": kernel, "kernel_ms": k_ms, "launches_per_step": n_k,
                          "kernel_ms_per_step": k_ms_step, "integrator_ms_per_step": sum(integ_ms) / len(integ_ms),
                          "bytes_per_ray": bytes_per_ray, "nodes_per_ray": cs.node_visits / cs.rays,
                          "tris_per_ray": cs.tri_tests / cs.rays,
                          "achieved_over_integrator": bytes_per_ray * rays[-1] / (sum(integ_ms) / len(integ_ms) * 1e-3) / 1e9,
-                         "note": "algorithmic node+triangle bytes (32 B per node visit, 48 B per triangle test). The scene is "
+                         "issue_bound": {"source": "profiles/r1_wide_wf_trace_1pipe_ncu.md (one mid-render launch owning the GPU)",
+                                         "issue_slots_busy_pct": 72.6, "alu_pipe_pct": 62.7, "fma_pipe_pct": 22.6, "lsu_wavefront_pct": 61.1,
+                                         "active_lanes_per_instruction": 15.9, "warp_instructions_per_ray": 114},
+                         "note": "algorithmic node+triangle bytes (64 B per 4-wide node visit, 48 B per triangle test). The scene is "
                                  "L1/L2-resident, so this is on-chip traffic expressed against the HBM copy peak; the binding limit "
                                  "is issue slots under divergence (DESIGN.md, profiles/). In wavefront mode 3 pipes overlap their "
                                  "wf_trace launches, so the per-launch average shares the GPU; achieved_over_integrator divides by "

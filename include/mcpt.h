@@ -100,6 +100,8 @@ typedef struct mcpt_stats {
     float integrate_ms;    /* CUDA-event time of the integrator alone: the megakernel, or the whole wavefront loop */
     float trace_ms;        /* wavefront mode: summed CUDA-event time of the wf_trace launches (the dominant kernel) */
     int32_t trace_launches;/* wavefront mode: number of wf_trace launches (= loop iterations) */
+    int32_t build_launches;/* kernels launched by the last mcpt_build_bvh (ours + CUB's) */
+    int32_t reserved;
 } mcpt_stats;
 
 enum { MCPT_MODE_MEGAKERNEL = 0, MCPT_MODE_WAVEFRONT = 1 };

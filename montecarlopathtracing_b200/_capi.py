@@ -42,7 +42,7 @@ class Hit(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("samples", C.c_double), ("rays", C.c_double), ("node_visits", C.c_double), ("tri_tests", C.c_double),
                 ("render_ms", C.c_float), ("build_ms", C.c_float), ("kernel_launches", C.c_int32), ("integrate_ms", C.c_float),
-                ("trace_ms", C.c_float), ("trace_launches", C.c_int32)]
+                ("trace_ms", C.c_float), ("trace_launches", C.c_int32), ("build_launches", C.c_int32), ("reserved", C.c_int32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if not k.startswith("_")}

@@ -49,6 +49,7 @@ struct mcpt_ctx {
     char* h_pin[PIN_RING] = {}; cudaEvent_t pin_ev[PIN_RING] = {};   // pinned ring of mcpt_ingest_obj_file (one buffer per reader thread)
     int last_ingest_launches = 0;
     float last_build_ms = 0.f;
+    int last_build_launches = 0;
     bool scene_loaded = false;
 };
 
@@ -499,6 +500,7 @@ MCPT_API int mcpt_build_bvh(mcpt_ctx* c, float* ms_out) {
     CU(cudaEventSynchronize(c->ev1));
     CU(cudaEventElapsedTime(&c->last_build_ms, c->ev0, c->ev1));
     if (ms_out) *ms_out = c->last_build_ms;
+    c->last_build_launches = launches;
 #if MCPT_WIDE
     unsigned w4[4] = {0, 0, 0, 0};
     CU(cudaMemcpy(w4, c->sb.w4_ctr, sizeof(w4), cudaMemcpyDeviceToHost));
@@ -556,7 +558,7 @@ namespace {
 void fill_stats(mcpt_ctx* c, mcpt_stats* st, double samples, const unsigned long long cnt[3], float ms, int launches) {
     if (!st) return;
     st->samples = samples; st->rays = (double)cnt[0]; st->node_visits = (double)cnt[1]; st->tri_tests = (double)cnt[2];
-    st->render_ms = ms; st->build_ms = c->last_build_ms; st->kernel_launches = launches; st->integrate_ms = 0.f;
+    st->render_ms = ms; st->build_ms = c->last_build_ms; st->build_launches = c->last_build_launches; st->reserved = 0; st->kernel_launches = launches; st->integrate_ms = 0.f;
     st->trace_ms = 0.f; st->trace_launches = 0;
 }
 // generateImg's camera basis (MTPC/pathTracing.cpp:276-294), in double on the host

@@ -27,7 +27,7 @@ def test_header_symbols_are_exported_and_bound(built_lib):
 
 def test_struct_sizes_match_header(built_lib):
     assert ctypes.sizeof(_capi.Material) == 72 and ctypes.sizeof(_capi.Light) == 32 and ctypes.sizeof(_capi.Camera) == 88
-    assert ctypes.sizeof(_capi.Hit) == 20 and ctypes.sizeof(_capi.Stats) == 56 and ctypes.sizeof(_capi.SceneDesc) == 72
+    assert ctypes.sizeof(_capi.Hit) == 20 and ctypes.sizeof(_capi.Stats) == 64 and ctypes.sizeof(_capi.SceneDesc) == 72
 
 
 def test_no_cpu_fallback(built_lib):
