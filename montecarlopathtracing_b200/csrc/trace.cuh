@@ -18,9 +18,7 @@ namespace mcpt {
 struct Hit { float t, u, v; int k; };  // k = sorted-leaf index, -1 = miss
 
 #define MCPT_STACK_SIZE 64   // arrays are declared with MCPT_STACK_SIZE + 4 entries (node4_step's branch-free pushes)
-#ifndef MCPT_WIDE_SORT
-#define MCPT_WIDE_SORT 1
-#endif
+
 // Edge tolerance of the FP32 barycentric test.  The reference's FP64 same-side test is inclusive (>= 0), so a ray
 // through a shared edge hits one of the two triangles; in FP32 the rounding of u, v can put it just outside BOTH
 // (a crack: the image diagonals of cornell-box run exactly along wall edges).  Accepting |excess| <= 2e-6 closes the
@@ -28,6 +26,8 @@ struct Hit { float t, u, v; int k; };  // k = sorted-leaf index, -1 = miss
 #define MCPT_EDGE_EPS 2.0e-6f
 
 __device__ __forceinline__ bool a_pos(float a) { return !(a < 0.0f); }
+// MUFU.RCP alone (1 ulp) instead of the IEEE reciprocal's 8-instruction sequence; both integrators and seam 2 share it.
+__device__ __forceinline__ float __frcp_approx(const float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
 // Per-ray constants.  Slab planes come from the 16-bit grid of the quantised nodes: a plane with grid coordinate q is
 // crossed at t = (origin + q*cell - o) / d = q*a + b with a = cell/d, b = (origin - o)/d.  q is turned into a float by
@@ -94,17 +94,24 @@ __device__ __forceinline__ void node_step(const QNode* __restrict__ nodes, int& 
 
 // One 4-wide node step (QNode4): four 16-B loads, four independent slab tests, then the hit children in near-to-far order —
 // the nearest is descended into, the others are pushed farthest first.  Order keys: the entry distance's float bits
-// (>= 0, so unsigned order = float order) with the slot number in the two low mantissa bits; a miss is 0xFFFFFFFF.
+// (>= 0, so unsigned order = float order); a miss is 0xFFFFFFFF and sorts last.  Keys and child references are sorted as
+// PAIRS (one compare + four selects per exchange): cheaper than sorting slot-tagged keys and picking the reference of every
+// sorted slot afterwards.  The pushes are predicated stores, not branches (ncu source view: the three branchy push blocks
+// ran on nearly every step for 2-6 of 32 lanes, ~40 of the step's ~150 instructions).
 __device__ __forceinline__ unsigned slab_key(const uint4 k, const RayCtx& r, const unsigned fx, const unsigned fy, const unsigned fz,
-                                             const float best_t, const unsigned slot) {
+                                             const float best_t) {
     const float nx = fmaf(q_sel(k.x, r.sx), r.ax, r.bx), gx = fmaf(q_sel(k.x, fx), r.ax, r.bx);
     const float ny = fmaf(q_sel(k.y, r.sy), r.ay, r.by), gy = fmaf(q_sel(k.y, fy), r.ay, r.by);
     const float nz = fmaf(q_sel(k.z, r.sz), r.az, r.bz), gz = fmaf(q_sel(k.z, fz), r.az, r.bz);
     const float cmin = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
     const float cmax = fminf(fminf(gx, gy), fminf(gz, best_t));
-    return cmin <= cmax ? ((__float_as_uint(cmin) & ~3u) | slot) : 0xFFFFFFFFu;
+    return cmin <= cmax ? __float_as_uint(cmin) : 0xFFFFFFFFu;
 }
-__device__ __forceinline__ void key_cswap(unsigned& a, unsigned& b) { const unsigned lo = min(a, b), hi = max(a, b); a = lo; b = hi; }
+__device__ __forceinline__ void pair_cswap(unsigned& ka, int& ra, unsigned& kb, int& rb) {
+    const bool p = kb < ka;
+    const unsigned k = p ? kb : ka; kb = p ? ka : kb; ka = k;
+    const int r = p ? rb : ra; rb = p ? ra : rb; ra = r;
+}
 template <bool COUNT>
 __device__ __forceinline__ void node4_step(const QNode4* __restrict__ nodes, int& node, const RayCtx& r, const float best_t,
                                            int* stack, int& sp, unsigned& n_nodes) {
@@ -114,33 +121,16 @@ __device__ __forceinline__ void node4_step(const QNode4* __restrict__ nodes, int
     const uint4 k3 = __ldg(&nodes[node].c[3]);
     if (COUNT) n_nodes++;
     const unsigned fx = r.sx ^ 0x0022u, fy = r.sy ^ 0x0022u, fz = r.sz ^ 0x0022u;
-    unsigned s0 = slab_key(k0, r, fx, fy, fz, best_t, 0u), s1 = slab_key(k1, r, fx, fy, fz, best_t, 1u);
-    unsigned s2 = slab_key(k2, r, fx, fy, fz, best_t, 2u), s3 = slab_key(k3, r, fx, fy, fz, best_t, 3u);
-    auto child = [&](const unsigned key) { return (int)((key & 2u) ? ((key & 1u) ? k3.w : k2.w) : ((key & 1u) ? k1.w : k0.w)); };
-    // pushes are predicated branches, not unconditional stores: most steps push nothing, and every local store is an L1
-    // wavefront (measured: branch-free pushes 1629 -> 1533 Msamples/s on cornell-box)
-#if MCPT_WIDE_SORT
-    key_cswap(s0, s1); key_cswap(s2, s3); key_cswap(s0, s2); key_cswap(s1, s3); key_cswap(s1, s2);
-    if (s0 == 0xFFFFFFFFu) { node = stack[--sp]; return; }
-    node = child(s0);
-    if (s1 != 0xFFFFFFFFu) {
-        if (s3 != 0xFFFFFFFFu && sp < MCPT_STACK_SIZE) stack[sp++] = child(s3);
-        if (s2 != 0xFFFFFFFFu && sp < MCPT_STACK_SIZE) stack[sp++] = child(s2);
-        if (sp < MCPT_STACK_SIZE) stack[sp++] = child(s1);
-    }
-#else
-    // only the nearest hit child is singled out; the other hit children are pushed in slot order (traversal results do not
-    // depend on the order)
-    const unsigned sm = min(min(s0, s1), min(s2, s3));
-    if (sm == 0xFFFFFFFFu) { node = stack[--sp]; return; }
-    node = child(sm);
-    {
-        if (s3 != sm && s3 != 0xFFFFFFFFu && sp < MCPT_STACK_SIZE) stack[sp++] = (int)k3.w;
-        if (s2 != sm && s2 != 0xFFFFFFFFu && sp < MCPT_STACK_SIZE) stack[sp++] = (int)k2.w;
-        if (s1 != sm && s1 != 0xFFFFFFFFu && sp < MCPT_STACK_SIZE) stack[sp++] = (int)k1.w;
-        if (s0 != sm && s0 != 0xFFFFFFFFu && sp < MCPT_STACK_SIZE) stack[sp++] = (int)k0.w;
-    }
-#endif
+    unsigned s0 = slab_key(k0, r, fx, fy, fz, best_t), s1 = slab_key(k1, r, fx, fy, fz, best_t);
+    unsigned s2 = slab_key(k2, r, fx, fy, fz, best_t), s3 = slab_key(k3, r, fx, fy, fz, best_t);
+    int r0 = (int)k0.w, r1 = (int)k1.w, r2 = (int)k2.w, r3 = (int)k3.w;
+    pair_cswap(s0, r0, s1, r1); pair_cswap(s2, r2, s3, r3); pair_cswap(s0, r0, s2, r2); pair_cswap(s1, r1, s3, r3); pair_cswap(s1, r1, s2, r2);
+    sp = min(sp, MCPT_STACK_SIZE);   // the array has 4 spare entries: the three pushes below need no bounds test
+    if (s3 != 0xFFFFFFFFu) { stack[sp] = r3; sp++; }
+    if (s2 != 0xFFFFFFFFu) { stack[sp] = r2; sp++; }
+    if (s1 != 0xFFFFFFFFu) { stack[sp] = r1; sp++; }
+    node = r0;
+    if (s0 == 0xFFFFFFFFu) node = stack[--sp];
 }
 
 // Möller–Trumbore on sorted triangle k; keeps it in `best` if it is the closer hit (ties: lower leaf index).
@@ -152,7 +142,7 @@ __device__ __forceinline__ void tri_test(const TriGeom* __restrict__ tris, const
     if (COUNT) n_tris++;
     const float3 E1 = f3(e1), E2 = f3(e2);
     const float3 pvec = cross(r.d, E2);
-    const float inv_det = 1.0f / dot(E1, pvec);  // det == 0 -> inf/NaN -> every comparison below fails
+    const float inv_det = __frcp_approx(dot(E1, pvec));  // det == 0 -> inf/NaN -> every comparison below fails
     const float3 tvec = r.o - f3(v0);
     const float u = dot(tvec, pvec) * inv_det;
     const float3 qvec = cross(tvec, E1);
@@ -162,7 +152,9 @@ __device__ __forceinline__ void tri_test(const TriGeom* __restrict__ tris, const
         // quirk Q2 in full: the reference keeps a hit only if t = (p.x - o.x)/d.x > 0 with p.x = o.x + d.x*t formed in
         // FP64 (MTPC/pathTracing.cpp:347,355); when |d.x*t| is below half an ulp of o.x that is 0 and the hit is
         // dropped.  Candidates that pass the FP32 test are rare (1-2 per ray), so the FP64 check is cheap.
-        if (__dadd_rn((double)r.o.x, __dmul_rn((double)r.d.x, (double)t)) != (double)r.o.x) {
+        // FP32 shortcut: |d.x*t| > 1e-12 |o.x| is ~1e4 FP64 ulps of o.x, so the FP64 sum certainly differs; the FP64 test runs
+        // only for the few candidates at grazing d.x.
+        if (fabsf(r.d.x * t) > 1.0e-12f * fabsf(r.o.x) || __dadd_rn((double)r.o.x, __dmul_rn((double)r.d.x, (double)t)) != (double)r.o.x) {
             best.t = t; best.u = u; best.v = v; best.k = k;
         }
     }
