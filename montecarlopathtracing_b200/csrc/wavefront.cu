@@ -339,9 +339,14 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
             }
         }
         const bool has_p = pend != 0;
-        const bool blocked = has_p && node < 0;   // a second leaf, or nothing left but the parked one
-        const unsigned pm = __ballot_sync(0xffffffffu, has_p), bm = __ballot_sync(0xffffffffu, blocked);
-        const unsigned nm = __ballot_sync(0xffffffffu, node >= 0);
+        // leaf_min <= 1 (the default): the triangle phase runs whenever a lane holds a leaf — measured as good as any
+        // threshold (sweeps in DESIGN.md) and it needs no ballots
+        unsigned pm = 0xffffffffu, bm = 0u, nm = 0u;
+        if (leaf_min > 1 || COUNT) {
+            const bool blocked = has_p && node < 0;   // a second leaf, or nothing left but the parked one
+            pm = __ballot_sync(0xffffffffu, has_p); bm = __ballot_sync(0xffffffffu, blocked);
+            nm = __ballot_sync(0xffffffffu, node >= 0);
+        }
         if (COUNT && lane == 0) { w_iter++; if (pm != 0u && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) w_tri++; }
         if (has_p && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) {
             leaf_test<COUNT>(sc.tri, pend, r, best, n_tris);
@@ -442,8 +447,8 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
 
     const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
     const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 16) / pipes;   // CTAs of 4 warps, shared by the pipes
-    const int refill_min = env_int("MCPT_REFILL_MIN", 12), leaf_min = env_int("MCPT_LEAF_MIN", 12),
-              block_min = env_int("MCPT_BLOCK_MIN", 4), node_steps = env_int("MCPT_NODE_STEPS", MCPT_WIDE ? 2 : 4);
+    const int refill_min = env_int("MCPT_REFILL_MIN", 12), leaf_min = env_int("MCPT_LEAF_MIN", 1),
+              block_min = env_int("MCPT_BLOCK_MIN", 1), node_steps = env_int("MCPT_NODE_STEPS", MCPT_WIDE ? 2 : 4);
     const int batch = 8;
     const bool diag = getenv("MCPT_DIAG_ALIVE") != nullptr;
     int nlaunch = 0, n_timed = 0;
