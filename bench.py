@@ -31,7 +31,7 @@ WORKLOADS = {
 # DRAM bytes of ONE launch of the dominant kernel from the committed `ncu --set full` capture (bytes; per launch like
 # roofline.achieved).  ~89 MB (ray queue in, hit records out) against ~1.4 GB of algorithmic node+triangle bytes per launch: the
 # scene is served from L1/L2.
-NCU_TRAFFIC = {("cornell-box-1024x1024-spp256", "wavefront"): 79.520256e6 + 10.336000e6,
+NCU_TRAFFIC = {("cornell-box-1024x1024-spp256", "wavefront"): 81.129984e6 + 9.479680e6,
                ("cornell-box-1024x1024-spp256", "megakernel"): 6.414592e6 + 64.855552e6}
 SYNTHETIC_TRIS = {"synthetic-5M": 5_000_000, "synthetic-1M": 1_000_000}
 DEFAULT_WORKLOAD = "cornell-box-1024x1024-spp256"
@@ -333,8 +333,8 @@ def run_ours(args):
                          "tris_per_ray": cs.tri_tests / cs.rays,
                          "achieved_over_integrator": bytes_per_ray * rays[-1] / (sum(integ_ms) / len(integ_ms) * 1e-3) / 1e9,
                          "issue_bound": {"source": "profiles/r1_wide_wf_trace_1pipe_ncu.md (one mid-render launch owning the GPU)",
-                                         "issue_slots_busy_pct": 72.6, "alu_pipe_pct": 62.7, "fma_pipe_pct": 22.6, "lsu_wavefront_pct": 61.1,
-                                         "active_lanes_per_instruction": 15.9, "warp_instructions_per_ray": 114},
+                                         "issue_slots_busy_pct": 69.5, "alu_pipe_pct": 60.3, "fma_pipe_pct": 23.3, "lsu_wavefront_pct": 67.4,
+                                         "active_lanes_per_instruction": 17.3, "warp_instructions_per_ray": 100},
                          "note": "algorithmic node+triangle bytes (64 B per 4-wide node visit, 48 B per triangle test). The scene is "
                                  "L1/L2-resident, so this is on-chip traffic expressed against the HBM copy peak; the binding limit "
                                  "is issue slots under divergence (DESIGN.md, profiles/). In wavefront mode 3 pipes overlap their "

@@ -2,6 +2,8 @@
 
   python tools/ncu_summary.py launches <launches.csv> <out.md>     per-kernel totals of a gpu__time_duration launch list
   python tools/ncu_summary.py metrics <report.ncu-rep> <out.md>    key counters of every profiled launch in a --set full report
+  python tools/ncu_summary.py source <report.ncu-rep> <out.md>     per-instruction execution counts of the first launch (source
+                                                                   view): share and active lanes per 20-instruction segment, opcode mix
 """
 import collections
 import csv
@@ -62,5 +64,37 @@ def metrics(src, dst):
                 for v, h in top) + "\n")
 
 
+def source(src, dst, seg=20):
+    raw = subprocess.run(["ncu", "-i", src, "--page", "source", "--csv", "--print-source", "sass"], stdout=subprocess.PIPE, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    name = rows[0][1] if rows and len(rows[0]) > 1 else "?"
+    hdr = rows[1]
+    isrc, ie, it, iss = hdr.index("Source"), hdr.index("Instructions Executed"), hdr.index("Thread Instructions Executed"), hdr.index("# Samples")
+    data = []
+    for r in rows[2:]:
+        if len(r) < 10 or r[0] == "Kernel Name":
+            break
+        if r[0] != "Address":
+            data.append((r[isrc].strip(), int(r[ie]), int(r[it]), int(r[iss])))
+    tot = sum(d[1] for d in data)
+    ops = collections.Counter()
+    for s_, e, _, _ in data:
+        tok = s_.split()
+        op = tok[1] if tok and tok[0].startswith("@") and len(tok) > 1 else (tok[0] if tok else "?")
+        ops[op.split(".")[0]] += e
+    with open(dst, "w") as f:
+        f.write("# ncu source view: executed warp instructions per SASS segment\n\nSource: `%s`, first launch of `%s`: %d SASS instructions, "
+                "%d warp instructions executed, %.1f active lanes per instruction.\n\n" %
+                (src, short(name), len(data), tot, sum(d[2] for d in data) / max(tot, 1)))
+        f.write("Opcode mix (share of executed warp instructions): " + ", ".join("%s %.1f %%" % (k, 100 * v / tot) for k, v in ops.most_common(14)) + "\n\n")
+        f.write("| SASS instructions | share | active lanes | stall samples | first instruction |\n|---|---:|---:|---:|---|\n")
+        for k in range(0, len(data), seg):
+            g = data[k:k + seg]
+            e = sum(d[1] for d in g)
+            if e * 1000 < tot:
+                continue
+            f.write("| %d-%d | %.1f %% | %.1f | %d | `%s` |\n" % (k, k + len(g) - 1, 100 * e / tot, sum(d[2] for d in g) / max(e, 1), sum(d[3] for d in g), g[0][0][:48]))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "metrics": metrics}[sys.argv[1]](sys.argv[2], sys.argv[3])
+    {"launches": launches, "metrics": metrics, "source": source}[sys.argv[1]](sys.argv[2], sys.argv[3])
