@@ -252,3 +252,43 @@ def test_wide_tree_small_counts(gpu_ctx, n):
         assert len(nodes) == 1 and r[0] == ~0 and r[1] == ~0
         return
     check_wide_tree(nodes, origin.astype(np.float64), cell.astype(np.float64), n, p.min(axis=1), p.max(axis=1))
+
+
+def test_wide_tree_large_mesh(gpu_ctx):
+    """1 M triangles: more wide nodes than the collapse kernel has resident threads, so its threads walk several entries
+    each (the multi-round path of wide.cu); same invariants, plus traversal against brute force on a few rays."""
+    n = 1 << 20
+    desc, keep = random_soup(n, seed=11, extent=2.4)
+    gpu_ctx.upload_scene(desc)
+    gpu_ctx.build_bvh()
+    _, _, face_sorted = gpu_ctx.get_morton()
+    nodes, origin, cell = gpu_ctx.get_wide_tree()
+    p = keep[0].reshape(n, 3, 3)[face_sorted].astype(np.float32).astype(np.float64)
+    n_wide = check_wide_tree(nodes, origin.astype(np.float64), cell.astype(np.float64), n, p.min(axis=1), p.max(axis=1))
+    assert 0.3 * n < n_wide < 0.55 * n
+    # closest hit of 64 rays through the cloud vs a brute-force Möller–Trumbore in FP64 over all triangles
+    rng = np.random.default_rng(3)
+    o = rng.uniform(0.0, 3.0, size=(64, 3)); d = rng.normal(size=(64, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.concatenate([o, d], axis=1).astype(np.float32)
+    hits = gpu_ctx.trace(rays)
+    tri = keep[0].reshape(n, 3, 3)
+    v0, e1, e2 = tri[:, 0], tri[:, 1] - tri[:, 0], tri[:, 2] - tri[:, 0]
+    for i in range(64):
+        oo, dd = rays[i, :3].astype(np.float64), rays[i, 3:].astype(np.float64)
+        pv = np.cross(dd, e2); det = np.einsum("ij,ij->i", e1, pv)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            inv = 1.0 / det
+            tv = oo - v0
+            u = np.einsum("ij,ij->i", tv, pv) * inv
+            qv = np.cross(tv, e1)
+            v = (qv @ dd) * inv
+            t = np.einsum("ij,ij->i", e2, qv) * inv
+        ok = (u >= 0) & (v >= 0) & (u + v <= 1) & (t > 0) & np.isfinite(t)
+        if not ok.any():
+            assert hits["tri"][i] < 0 or hits["t"][i] > 0     # a grazing edge hit the FP64 test excludes is tolerated
+            continue
+        best = np.flatnonzero(ok)[np.argmin(t[ok])]
+        if hits["tri"][i] != best:                            # only a near-tie may differ
+            assert hits["tri"][i] >= 0 and abs(hits["t"][i] - t[best]) <= 1e-4 * t[best], (i, hits["tri"][i], best)
+        else:
+            assert abs(hits["t"][i] - t[best]) <= 1e-5 * max(t[best], 1e-3)
