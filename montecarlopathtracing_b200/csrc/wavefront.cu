@@ -446,7 +446,7 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
     for (int k = 1; k < pipes; k++) WF_CU(cudaStreamWaitEvent(pp[k].st, ev_fork, 0));
 
     const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
-    const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 16) / pipes;   // CTAs of 4 warps, shared by the pipes
+    const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 12) / pipes;   // CTAs of 4 warps, shared by the pipes
     const int refill_min = env_int("MCPT_REFILL_MIN", 12), leaf_min = env_int("MCPT_LEAF_MIN", 1),
               block_min = env_int("MCPT_BLOCK_MIN", 1), node_steps = env_int("MCPT_NODE_STEPS", MCPT_WIDE ? 2 : 4);
     const int batch = 8;
