@@ -784,6 +784,7 @@ MCPT_API int64_t mcpt_png_size(int width, int height) {
 
 MCPT_API int mcpt_encode_png(mcpt_ctx* c, const float* d_rgb, int width, int height, uint8_t* png_out, int64_t capacity) {
     if (!c || !d_rgb || !png_out || width <= 0 || height <= 0) return fail_arg("mcpt_encode_png: bad argument");
+    if (width > 21844) return fail_arg("mcpt_encode_png: width > 21844 does not fit svpng's one-block-per-scanline framing");
     const size_t bytes = png_encoded_size(width, height);
     if (capacity < (int64_t)bytes) return fail_arg("mcpt_encode_png: output buffer smaller than mcpt_png_size()");
     CU(cudaSetDevice(c->device));

@@ -1,6 +1,7 @@
 // png_device.cu — the output stage on the GPU: imshow's quantisation
 // (uchar)clamp(v*255, 0, 255) (MTPC/MTPC.cpp:22-30) and the uncompressed-PNG framing that MTPC/svpng.inc:77-108 emits
-// with one fputc per byte, byte-identical to the host writer (host/png_writer.cpp).  At 3840x2160 the host stage
+// with one fputc per byte — the same bytes svpng writes (one stored block per scanline; tests compare with a file the
+// reference wrote) and the host writer (host/png_writer.cpp).  At 3840x2160 the host stage
 // costs as much as an 8-GPU render of the image; here the float image never leaves the device: the D2H copy is the
 // finished PNG (1 byte per channel instead of 4).
 //   K13 png_pack_kernel   one thread per raw scanline byte: filter byte / quantised channel into its place inside the
@@ -19,8 +20,8 @@ namespace mcpt {
 
 struct PngLayout {
     unsigned long long raw;      // (3w+1)*h scanline bytes
-    unsigned long long nblocks;  // stored deflate blocks of <= 65535 bytes
-    unsigned long long zsize;    // 2 + 5*nblocks + raw + 4
+    unsigned long long nblocks;  // stored deflate blocks: ONE PER SCANLINE, as svpng writes them (MTPC/svpng.inc:98-105)
+    unsigned long long zsize;    // 2 + h*(5 + 3w+1) + 4  (svpng.inc:96)
     unsigned long long total;    // 8 + 25 + 12 + zsize + 12
     unsigned long long idat_tag; // offset of "IDAT"
     unsigned long long zoff;     // offset of the zlib stream
@@ -29,7 +30,7 @@ struct PngLayout {
 __host__ __device__ inline PngLayout png_layout(int w, int h) {
     PngLayout L;
     L.raw = (3ull * (unsigned long long)w + 1ull) * (unsigned long long)h;
-    L.nblocks = (L.raw + 65534ull) / 65535ull;
+    L.nblocks = (unsigned long long)h;
     L.zsize = 2ull + 5ull * L.nblocks + L.raw + 4ull;
     L.idat_tag = 8ull + 25ull + 4ull;
     L.zoff = L.idat_tag + 4ull;
@@ -51,16 +52,15 @@ __global__ void __launch_bounds__(256) png_pack_kernel(const float* __restrict__
             d = d < 0.0 ? 0.0 : (d > 255.0 ? 255.0 : d);
             v = d == d ? (unsigned)d : 0u;                                    // truncation; NaN -> 0
         }
-        const unsigned long long blk = i / 65535ull, in_blk = i - blk * 65535ull;
-        unsigned char* z = png + L.zoff + 2ull + 5ull * (blk + 1ull) + i;
+        unsigned char* z = png + L.zoff + 2ull + 5ull * (y + 1ull) + i;   // scanline y sits behind y+1 block headers
         *z = (unsigned char)v;
-        if (in_blk == 0) {   // this thread also writes its block's 5-byte header
-            const unsigned long long len = L.raw - i < 65535ull ? L.raw - i : 65535ull;
-            z[-5] = (blk + 1ull == L.nblocks) ? 1 : 0;
-            z[-4] = (unsigned char)len; z[-3] = (unsigned char)(len >> 8);
-            z[-2] = (unsigned char)(~len); z[-1] = (unsigned char)((~len) >> 8);
+        if (c == 0) {   // the filter byte's thread also writes its scanline's 5-byte stored-block header
+            z[-5] = (y + 1ull == (unsigned long long)h) ? 1 : 0;
+            z[-4] = (unsigned char)row; z[-3] = (unsigned char)(row >> 8);
+            z[-2] = (unsigned char)(~row); z[-1] = (unsigned char)((~row) >> 8);
         }
-        s1 += v; s2 += (L.raw - i) * v;
+        // the weight is reduced mod 65521 first, so the 64-bit sums cannot overflow for any image the 32-bit IDAT length allows
+        s1 += v; s2 += ((L.raw - i) % 65521ull) * v;
     }
     // integer sums: order-independent, so the block reduction + atomics are deterministic
     for (int off = 16; off > 0; off >>= 1) { s1 += __shfl_down_sync(0xffffffffu, s1, off); s2 += __shfl_down_sync(0xffffffffu, s2, off); }
@@ -151,7 +151,7 @@ size_t png_encoded_size(int w, int h) { return (size_t)png_layout(w, h).total; }
 // d_png: png_encoded_size bytes; d_scratch: 32 bytes (two 64-bit sums + the CRC word).  4 launches on `stream`.
 int launch_png_encode(const float* d_rgb, int w, int h, unsigned char* d_png, void* d_scratch, cudaStream_t stream) {
     const PngLayout L = png_layout(w, h);
-    if (L.zsize > 0xffffffffull) return (int)cudaErrorInvalidValue;   // IDAT length is 32 bits
+    if (L.zsize > 0xffffffffull || 3ull * w + 1ull > 65535ull) return (int)cudaErrorInvalidValue;   // IDAT length is 32 bits, a block's LEN 16
     cudaError_t e = cudaMemsetAsync(d_scratch, 0, 32, stream);
     if (e != cudaSuccess) return (int)e;
     unsigned long long* sums = (unsigned long long*)d_scratch;

@@ -1,7 +1,8 @@
 // 8-bit RGB PNG output: the reference's imshow quantisation (MTPC/MTPC.cpp:22-30:
-// (uchar)clamp(v*255, 0, 255), truncation, no gamma) followed by an uncompressed PNG stream
-// (what MTPC/svpng.inc:77-108 emits byte by byte with fputc; here built in memory, written once,
-// and the file is closed — the reference never fcloses, which truncated its veach-mis renders).
+// (uchar)clamp(v*255, 0, 255), truncation, no gamma) followed by the uncompressed PNG stream
+// MTPC/svpng.inc:77-108 emits byte by byte with fputc — the SAME bytes (one stored deflate block per
+// scanline, tests/test_host.py compares with a file the reference wrote); here built in memory, written
+// once, and the file is closed — the reference never fcloses, which truncated its veach-mis renders.
 #include <cstdint>
 #include <cstdio>
 #include <string>
@@ -48,6 +49,8 @@ void quantize_rgb(const float* rgb, size_t n, uint8_t* out) {
 
 extern "C" MCPT_API int mcpt_write_png(const char* file, const float* rgb, int width, int height) {
     if (!file || !rgb || width <= 0 || height <= 0) { mcpt_set_error("mcpt_write_png: bad argument"); return MCPT_ERR_ARG; }
+    // svpng stores a scanline's 3w+1 bytes in one deflate block whose length field has 16 bits (MTPC/svpng.inc:100)
+    if (width > 21844) { mcpt_set_error("mcpt_write_png: width > 21844 does not fit svpng's one-block-per-scanline framing"); return MCPT_ERR_ARG; }
     const size_t row = size_t(width) * 3;
     // raw scanlines: filter byte 0 + RGB
     std::vector<uint8_t> raw((row + 1) * height);
@@ -55,18 +58,20 @@ extern "C" MCPT_API int mcpt_write_png(const char* file, const float* rgb, int w
         raw[(row + 1) * y] = 0;
         mcpt::quantize_rgb(rgb + row * y, row, &raw[(row + 1) * y + 1]);
     }
-    // zlib container with stored (uncompressed) deflate blocks of <= 65535 bytes
+    // zlib container exactly as svpng frames it (MTPC/svpng.inc:96-105): ONE stored deflate block per scanline
+    // (final-flag byte, LEN = 3w+1 and ~LEN little-endian, the filter byte 0, the row), IDAT length 2 + h*(5 + p) + 4
     std::vector<uint8_t> z;
-    z.reserve(raw.size() + raw.size() / 65535 * 5 + 16);
+    z.reserve(raw.size() + size_t(height) * 5 + 16);
     z.push_back(0x78); z.push_back(0x01);
     uint32_t a = 1, b = 0;
-    for (size_t off = 0; off < raw.size(); off += 65535) {
-        size_t len = raw.size() - off < 65535 ? raw.size() - off : 65535;
-        z.push_back(off + len == raw.size() ? 1 : 0);
-        z.push_back(uint8_t(len)); z.push_back(uint8_t(len >> 8));
-        z.push_back(uint8_t(~len)); z.push_back(uint8_t((~len) >> 8));
-        z.insert(z.end(), raw.begin() + off, raw.begin() + off + len);
-        for (size_t i = 0; i < len; i++) { a = (a + raw[off + i]) % 65521; b = (b + a) % 65521; }
+    const uint32_t p = uint32_t(row + 1);
+    for (int y = 0; y < height; y++) {
+        z.push_back(y == height - 1 ? 1 : 0);
+        z.push_back(uint8_t(p)); z.push_back(uint8_t(p >> 8));
+        z.push_back(uint8_t(~p)); z.push_back(uint8_t((~p) >> 8));
+        const uint8_t* line = &raw[size_t(p) * y];
+        z.insert(z.end(), line, line + p);
+        for (uint32_t i = 0; i < p; i++) { a = (a + line[i]) % 65521; b = (b + a) % 65521; }
     }
     be32(z, (b << 16) | a);
     std::vector<uint8_t> png = {0x89, 'P', 'N', 'G', '\r', '\n', 0x1A, '\n'};

@@ -154,13 +154,45 @@ def ref_trace(scene_base, rays):
             "pn": rec["d"][:, 4:7].copy()}
 
 
-def ref_image(scene_base, spp, width=0, height=0):
-    """generateImg of the unmodified reference; returns (image float64 HxWx3, wall ms of generateImg)."""
-    with tempfile.NamedTemporaryFile(suffix=".bin") as f:
-        err = _run_ref(["image", scene_base, spp, width, height, f.name])
-        raw = np.fromfile(f.name, np.uint8)
+def ref_image(scene_base, spp, width=0, height=0, with_png=False, threads=None):
+    """generateImg of the unmodified reference; returns (image float64 HxWx3, wall ms of generateImg) and, with_png, also the
+    bytes of the PNG the reference's own imshow + svpng (MTPC/MTPC.cpp:10-33) wrote for that image."""
+    with tempfile.TemporaryDirectory() as d:
+        out = os.path.join(d, "img.bin")
+        args = ["image", scene_base, spp, width, height, out]
+        if with_png:
+            args.append(os.path.join(d, "ref"))
+        err = _run_ref(args, threads=threads)
+        raw = np.fromfile(out, np.uint8)
+        png = open(os.path.join(d, "ref-SPP%d.png" % spp), "rb").read() if with_png else None
     w, h, _ = np.frombuffer(raw[:12], np.int32)
-    return np.frombuffer(raw[12:], np.float64).reshape(h, w, 3).copy(), _ms(err, "REF_IMAGE_MS")
+    img = np.frombuffer(raw[12:], np.float64).reshape(h, w, 3).copy()
+    return (img, _ms(err, "REF_IMAGE_MS"), png) if with_png else (img, _ms(err, "REF_IMAGE_MS"))
+
+
+def ref_png(img):
+    """imshow + svpng of the unmodified reference on a caller-supplied image (HxWx3 doubles) -> the PNG file's bytes."""
+    img = np.ascontiguousarray(img, np.float64)
+    h, w = img.shape[:2]
+    with tempfile.TemporaryDirectory() as d:
+        img.tofile(os.path.join(d, "in.bin"))
+        _run_ref(["png", w, h, os.path.join(d, "in.bin"), os.path.join(d, "ref"), 1])
+        return open(os.path.join(d, "ref-SPP1.png"), "rb").read()
+
+
+def ref_scene(scene_base):
+    """What the reference's read_scene parsed (MTPC/sceneManagement.cpp:76-189), per face in OBJ order:
+    pos (n,3,3), nrm (n,3,3), uv (n,3,2) float64 and the material names."""
+    with tempfile.NamedTemporaryFile(suffix=".bin") as f:
+        _run_ref(["scene", scene_base, f.name])
+        raw = open(f.name, "rb").read()
+    n = int(np.frombuffer(raw[:4], np.int32)[0])
+    geo, names, off = np.empty((n, 24)), [], 4
+    for i in range(n):
+        geo[i] = np.frombuffer(raw[off:off + 192], np.float64); off += 192
+        ln = int(np.frombuffer(raw[off:off + 4], np.int32)[0]); off += 4
+        names.append(raw[off:off + ln].decode()); off += ln
+    return geo[:, 0:9].reshape(n, 3, 3), geo[:, 9:18].reshape(n, 3, 3), geo[:, 18:24].reshape(n, 3, 2), names
 
 
 def ref_build_ms(scene_base, reps=5):

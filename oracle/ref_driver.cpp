@@ -7,6 +7,7 @@
 //   BVH::BVH                MTPC/BVH.cpp:37
 //   ray_intersect           MTPC/pathTracing.cpp:382
 //   generateImg             MTPC/pathTracing.cpp:274
+//   imshow (+ svpng)        MTPC/MTPC.cpp:10, MTPC/svpng.inc:77
 // The one deliberate difference from render_scene: std::stable_sort instead of std::sort
 // (MTPC/MTPC.cpp:44), which fixes the order inside runs of equal Morton codes.
 #include <chrono>
@@ -22,6 +23,7 @@
 #include "pathTracing.h"
 
 bool render_scene(std::string path, std::string filename, int N_ray_per_pixel);
+void imshow(double* SRC, int WIDTH, int HEIGHT, std::string filename, int N_ray_per_pixel);   // MTPC/MTPC.cpp:10
 
 using clk = std::chrono::steady_clock;
 static double ms_since(clk::time_point t0) { return std::chrono::duration<double, std::milli>(clk::now() - t0).count(); }
@@ -109,6 +111,44 @@ static int cmd_image(int argc, char** argv) {
     wr(f, img.img, sizeof(double) * 3 * (size_t)hdr[0] * hdr[1]);
     fclose(f);
     fprintf(stderr, "REF_IMAGE_MS %.3f w %d h %d spp %d\n", ms, hdr[0], hdr[1], spp);
+    // optional: the reference's own output stage on the same image -> <png_prefix>-SPP<spp>.png (never fclose'd by imshow;
+    // the normal process exit below flushes it)
+    if (argc > 7) imshow(img.img, scene.camera.width, scene.camera.height, argv[7], spp);
+    return 0;
+}
+
+// png <w> <h> <doubles_in> <png_prefix> <spp>: imshow + svpng on a caller-supplied double image (w*h*3 raw doubles).
+static int cmd_png(int argc, char** argv) {
+    if (argc < 7) return 1;
+    const int w = atoi(argv[2]), h = atoi(argv[3]);
+    std::vector<double> img(3 * (size_t)w * h);
+    FILE* fi = fopen(argv[4], "rb");
+    if (!fi) { perror(argv[4]); return 2; }
+    if (fread(img.data(), 8, img.size(), fi) != img.size()) return 2;
+    fclose(fi);
+    imshow(img.data(), w, h, argv[5], atoi(argv[6]));
+    return 0;
+}
+
+// scene <base> <out>: what read_scene parsed, per face in OBJ order: v1 v2 v3 (9 doubles), vn1 vn2 vn3 (9), vt1 vt2 vt3 (6),
+// then the material name as int32 length + bytes.  Header: int32 n.  (scene.f is NOT sorted here.)
+static int cmd_scene(int argc, char** argv) {
+    if (argc < 4) return 1;
+    scene_data scene;
+    scene.read_scene(argv[2]);
+    FILE* f = fopen(argv[3], "wb");
+    int32_t n = (int32_t)scene.f.size();
+    wr(f, &n, 4);
+    for (int i = 0; i < n; i++) {
+        Face& fc = scene.f[i];
+        double d[24] = {fc.v1.x, fc.v1.y, fc.v1.z, fc.v2.x, fc.v2.y, fc.v2.z, fc.v3.x, fc.v3.y, fc.v3.z,
+                        fc.vn1.x, fc.vn1.y, fc.vn1.z, fc.vn2.x, fc.vn2.y, fc.vn2.z, fc.vn3.x, fc.vn3.y, fc.vn3.z,
+                        fc.vt1.vtx, fc.vt1.vty, fc.vt2.vtx, fc.vt2.vty, fc.vt3.vtx, fc.vt3.vty};
+        wr(f, d, sizeof(d));
+        int32_t len = (int32_t)fc.material.size();
+        wr(f, &len, 4); wr(f, fc.material.data(), (size_t)len);
+    }
+    fclose(f);
     return 0;
 }
 
@@ -155,7 +195,8 @@ static int cmd_trace(int argc, char** argv) {
 int main(int argc, char** argv) {
     if (argc < 2) {
         fprintf(stderr, "usage: %s render <dir/> <name> <spp> | morton <base> <out> | buildtime <base> [reps] |\n"
-                        "       image <base> <spp> <w> <h> <out> | trace <base> <rays_in> <out>\n", argv[0]);
+                        "       image <base> <spp> <w> <h> <out> [png_prefix] | trace <base> <rays_in> <out> |\n"
+                        "       png <w> <h> <doubles_in> <png_prefix> <spp> | scene <base> <out>\n", argv[0]);
         return 1;
     }
     std::string c = argv[1];
@@ -164,5 +205,7 @@ int main(int argc, char** argv) {
     if (c == "buildtime") return cmd_buildtime(argc, argv);
     if (c == "image") return cmd_image(argc, argv);
     if (c == "trace") return cmd_trace(argc, argv);
+    if (c == "png") return cmd_png(argc, argv);
+    if (c == "scene") return cmd_scene(argc, argv);
     return 1;
 }

@@ -1,12 +1,21 @@
 """Generates the golden fixtures under tests/golden/ from the UNMODIFIED reference (oracle/_ref/mcpt_ref, built by
 oracle/build_ref.sh from /root/reference).  Run in the build container only (the GPU box has no /root/reference):
 
-    python tests/golden/make_golden.py [--images]
+    python tests/golden/make_golden.py [--base] [--images] [--configs] [--glass] [--png] [--scene-arrays]
 
 Fixtures (per scene S in cornell-box, veach-mis):
   S_morton.npz   codes (OBJ order, uint32), perm (stable-sorted leaf -> OBJ face), centroids (float32)
   S_rays.npz     rays (n,6 float64: camera, bounce and light-directed rays), reference hit/face/t/p/pn
   S_image.npz    two independent reference renders (time-seeded RNG) at reduced resolution + their wall ms
+--configs (tens of minutes on 8 cores): the BASELINE.json configs at their stated spp, as point-subsamples of the full image
+(the reference shoots one un-jittered ray through a pixel's corner, quirk Q4, so fewer pixels at the same camera are a
+subset of the full-resolution image with the same per-pixel estimator):
+  cornell-box_cfg2.npz   256 x 256 x 256 spp   (config 2: cornell-box at SPP=256)
+  veach-mis_cfg3.npz     300 x 225 x 100 spp   (config 3: veach-mis at SPP=100)
+  cornell-box_cfg5.npz   384 x 216 x 64 spp    (config 5's 16:9 aspect override, dx = dy*W/H, MTPC/pathTracing.cpp:280)
+--glass:  glass-box_image.npz  scenes/glass-box (Ni 1.5, tests/golden/make_glass_scene.py) 160 x 160 x 128 spp, two renders
+--png:    png_golden.npz       images (float32-representable doubles) + the bytes of the PNG the reference's imshow + svpng wrote
+--scene-arrays: S_scene.npz    what the reference's read_scene parsed (per-face v/vn/vt in OBJ order, material names)
 """
 import os
 import sys
@@ -66,9 +75,58 @@ def make_rays(scene, name, rng):
     return np.concatenate([prim, bounce, shadow, misc], axis=0).astype(np.float32).astype(np.float64)
 
 
+CONFIG_IMAGES = {"cornell-box_cfg2": ("cornell-box", 256, 256, 256), "veach-mis_cfg3": ("veach-mis", 300, 225, 100),
+                 "cornell-box_cfg5": ("cornell-box", 384, 216, 64)}
+
+
+def two_renders(scene, w, h, spp, out_name):
+    imgs, mss = [], []
+    for _ in range(2):
+        img, ms = O.ref_image(O.REF_SCENE_DIR + scene, spp, w, h)
+        assert np.array_equal(img, img.astype(np.float32).astype(np.float64))   # generateImg accumulates in float (:301,:322)
+        imgs.append(img.astype(np.float32)); mss.append(ms)
+        time.sleep(1.1)  # the reference seeds its RNG with time(NULL)
+    np.savez_compressed(os.path.join(OUT, out_name + ".npz"), a=imgs[0], b=imgs[1], spp=spp, ms=np.array(mss))
+    print(out_name, w, h, spp, "ms", mss, flush=True)
+
+
+def make_png_golden():
+    """Byte-parity fixtures for the output stage: the reference's own imshow + svpng on (1) a small reference render and
+    (2) hand-made images with negatives, values > 1, exact k/255 boundaries, 1 x 1 and a width whose 3w+1 crosses 256."""
+    rng = np.random.default_rng(7)
+    img, _, png = O.ref_image(O.REF_SCENE_DIR + "cornell-box", 4, 96, 64, with_png=True)
+    out = {"render_img": img.astype(np.float32), "render_png": np.frombuffer(png, np.uint8)}
+    assert O.ref_png(img) == png
+    cases = {"noise_7x5": rng.uniform(-0.3, 1.4, size=(5, 7, 3)), "one_1x1": np.array([[[0.5, 1.0, 0.25]]]),
+             "ramp_256x3": (np.arange(256 * 3 * 3).reshape(3, 256, 3) % 256) / 255.0,
+             "wide_300x2": rng.uniform(0, 1, size=(2, 300, 3)), "tall_1x70": rng.uniform(0, 2, size=(70, 1, 3))}
+    for k, v in cases.items():
+        v32 = v.astype(np.float32)
+        out[k + "_img"] = v32
+        out[k + "_png"] = np.frombuffer(O.ref_png(v32.astype(np.float64)), np.uint8)
+    np.savez_compressed(os.path.join(OUT, "png_golden.npz"), **out)
+    print("png_golden", {k: v.shape for k, v in out.items()})
+
+
 def main():
     if not O.have_ref():
         O.build()
+    if "--png" in sys.argv:
+        make_png_golden()
+    if "--scene-arrays" in sys.argv:
+        for name in ("cornell-box", "veach-mis", "glass-box"):
+            pos, nrm, uv, names = O.ref_scene(O.REF_SCENE_DIR + name)
+            uniq = sorted(set(names))
+            np.savez_compressed(os.path.join(OUT, name + "_scene.npz"), pos=pos, nrm=nrm, uv=uv, mat_names=np.array(uniq),
+                                mat_index=np.array([uniq.index(x) for x in names], np.int32))
+            print(name, "scene arrays", pos.shape)
+    if "--glass" in sys.argv:
+        two_renders("glass-box", 160, 160, 128, "glass-box_image")
+    if "--configs" in sys.argv:
+        for out_name, (scene, w, h, spp) in CONFIG_IMAGES.items():
+            two_renders(scene, w, h, spp, out_name)
+    if "--base" not in sys.argv and "--images" not in sys.argv:
+        return
     rng = np.random.default_rng(20261104)
     for name in ("cornell-box", "veach-mis"):
         scene = M.HostScene(os.path.join(ROOT, "scenes") + "/", name)

@@ -195,7 +195,7 @@ def test_wavefront_chunk_ranges_are_gpu_count_independent(gpu_ctx, scenes):
 @pytest.mark.parametrize("h,w", [(1, 1), (37, 301), (270, 480), (1080, 1920)])
 def test_device_png_stage_is_byte_identical_to_the_host_writer(gpu_ctx, tmp_path, h, w):
     """imshow + svpng on the GPU (K13-K15): quantisation (uchar)clamp(v*255,0,255) incl. negatives, > 1 and NaN, stored
-    deflate blocks (several per image above 65535 raw bytes), Adler-32 and both CRC-32s — the same bytes as
+    deflate blocks (one per scanline, as svpng frames them), Adler-32 and both CRC-32s — the same bytes as
     mcpt_write_png (whose output test_host.py checks against the reference's rule and a PNG decoder)."""
     import torch
     rng = np.random.default_rng(h * 10007 + w)
@@ -208,6 +208,20 @@ def test_device_png_stage_is_byte_identical_to_the_host_writer(gpu_ctx, tmp_path
     d = torch.from_numpy(img).cuda()
     got = gpu_ctx.encode_png(d.data_ptr(), w, h)
     assert len(got) == len(want) == M.png_size(w, h)
+    assert np.array_equal(got, want), "first differing byte at %d" % int(np.nonzero(got != want)[0][0])
+
+
+@pytest.mark.parametrize("case", ["render", "noise_7x5", "one_1x1", "ramp_256x3", "wide_300x2", "tall_1x70"])
+def test_device_png_stage_equals_the_reference_file(gpu_ctx, case):
+    """K13-K15 against files the UNMODIFIED reference's imshow + svpng wrote (tests/golden/png_golden.npz): every byte."""
+    import torch
+    from conftest import GOLDEN
+    g = np.load(os.path.join(GOLDEN, "png_golden.npz"))
+    img, want = np.ascontiguousarray(g[case + "_img"]), g[case + "_png"]
+    h, w = img.shape[:2]
+    d = torch.from_numpy(img).cuda()
+    got = gpu_ctx.encode_png(d.data_ptr(), w, h)
+    assert len(got) == len(want)
     assert np.array_equal(got, want), "first differing byte at %d" % int(np.nonzero(got != want)[0][0])
 
 

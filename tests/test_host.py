@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 import montecarlopathtracing_b200 as M
-from conftest import SCENES
+from conftest import GOLDEN, SCENES
 
 
 def _parse_obj_independently(path):
@@ -118,7 +118,7 @@ def _decode_png(path):
 def test_png_quantisation_matches_imshow(tmp_path):
     """(uchar)clamp(v*255, 0, 255): truncation, no gamma (MTPC/MTPC.cpp:26-28); file complete and closed."""
     rng = np.random.default_rng(0)
-    img = rng.uniform(-0.2, 1.4, size=(37, 301, 3)).astype(np.float32)   # > 65535 raw bytes -> several stored blocks
+    img = rng.uniform(-0.2, 1.4, size=(37, 301, 3)).astype(np.float32)   # one stored block per scanline
     img[0, 0] = [0.0, 1.0, 0.5]; img[0, 1] = [50.0, np.nan, 254.999 / 255]
     f = str(tmp_path / "x.png")
     M.write_png(f, img)
@@ -129,3 +129,28 @@ def test_png_quantisation_matches_imshow(tmp_path):
     from PIL import Image
     assert np.array_equal(np.asarray(Image.open(f)), want)
     assert os.path.getsize(f) == M.png_size(301, 37)
+
+
+PNG_CASES = ["render", "noise_7x5", "one_1x1", "ramp_256x3", "wide_300x2", "tall_1x70"]
+
+
+@pytest.mark.parametrize("case", PNG_CASES)
+def test_png_bytes_equal_the_reference_file(tmp_path, case):
+    """mcpt_write_png against files the UNMODIFIED reference's imshow + svpng wrote (tests/golden/png_golden.npz, made by
+    make_golden.py --png from oracle/_ref/mcpt_ref): same quantisation, one stored deflate block per scanline, IDAT length
+    2 + h*(5 + 3w+1) + 4, Adler-32 and CRCs (MTPC/MTPC.cpp:22-30, MTPC/svpng.inc:77-108) — every byte."""
+    g = np.load(os.path.join(GOLDEN, "png_golden.npz"))
+    img, want = g[case + "_img"], g[case + "_png"]
+    h, w = img.shape[:2]
+    f = str(tmp_path / "x.png")
+    M.write_png(f, img)
+    got = np.fromfile(f, np.uint8)
+    assert len(got) == len(want) == M.png_size(w, h) == 8 + 25 + 12 + 2 + h * (5 + 3 * w + 1) + 4 + 12
+    assert np.array_equal(got, want), "first differing byte at %d" % int(np.nonzero(got != want)[0][0])
+
+
+def test_png_size_of_the_shipped_resolutions():
+    """svpng's cornell-box file is 3 151 935 bytes (result/cornell-box-SPP*.png), veach-mis 3 245 463."""
+    assert M.png_size(1024, 1024) == 3151935 and M.png_size(1200, 900) == 3245463
+    with pytest.raises(M.McptError, match="21844"):
+        M.write_png("/tmp/never.png", np.zeros((1, 21845, 3), np.float32))
