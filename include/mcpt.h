@@ -144,8 +144,12 @@ MCPT_API int mcpt_write_png(const char* file, const float* rgb, int width, int h
 MCPT_API const char* mcpt_last_error(void);
 MCPT_API int mcpt_create(int device, mcpt_ctx** out);
 MCPT_API void mcpt_destroy(mcpt_ctx* ctx);
-/* Run on the caller's CUDA stream (a cudaStream_t passed as void*) instead of the context's own. */
+/* Run on the caller's CUDA stream (a cudaStream_t passed as void*) instead of the context's own.  The handle is used as
+ * given: NULL is CUDA's legacy default stream (stream 0, what torch.cuda.current_stream().cuda_stream is by default), NOT
+ * "back to the context's own stream" — that is mcpt_use_own_stream.  Work the caller enqueues on that stream before / after
+ * a call is ordered before / after the call's kernels; calls that return host data synchronise the stream themselves. */
 MCPT_API int mcpt_set_stream(mcpt_ctx* ctx, void* cuda_stream);
+MCPT_API int mcpt_use_own_stream(mcpt_ctx* ctx);
 /* Philox key salt (default 0). Images depend only on (seed, pixel, sample), never on GPU count. */
 MCPT_API int mcpt_set_seed(mcpt_ctx* ctx, uint64_t seed);
 

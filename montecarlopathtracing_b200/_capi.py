@@ -66,6 +66,7 @@ SIGNATURES = {
     "mcpt_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
     "mcpt_destroy": (None, [C.c_void_p]),
     "mcpt_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "mcpt_use_own_stream": (C.c_int, [C.c_void_p]),
     "mcpt_set_seed": (C.c_int, [C.c_void_p, C.c_uint64]),
     "mcpt_upload_scene": (C.c_int, [C.c_void_p, C.POINTER(SceneDesc)]),
     "mcpt_build_bvh": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),

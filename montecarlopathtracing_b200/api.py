@@ -104,6 +104,9 @@ class Context:
     def set_stream(self, cuda_stream_ptr):
         check(lib().mcpt_set_stream(self._c, C.c_void_p(cuda_stream_ptr)))
 
+    def use_own_stream(self):
+        check(lib().mcpt_use_own_stream(self._c))
+
     def set_seed(self, seed):
         check(lib().mcpt_set_seed(self._c, C.c_uint64(seed)))
 

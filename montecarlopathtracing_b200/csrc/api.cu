@@ -50,6 +50,7 @@ struct mcpt_ctx {
     int last_ingest_launches = 0;
     float last_build_ms = 0.f;
     int last_build_launches = 0;
+    int coop_blocks[2] = {0, 0};   // co-resident CTAs of wide_collapse_kernel / ploc_rounds_kernel on this device
     bool scene_loaded = false;
 };
 
@@ -115,7 +116,7 @@ int alloc_scene(mcpt_ctx* c, int n) {
     SceneBuffers& s = c->sb;
     s.n_faces = n;
     const size_t N = (size_t)n;
-    s.ploc_temp_bytes = ploc_scan_temp_bytes(n);
+    s.ploc_temp_bytes = ploc_scratch_bytes(n);
     s.cub_temp_bytes = lbvh_sort_temp_bytes(n);
     { const char* v = getenv("MCPT_BVH"); s.use_ploc = !(v && std::strcmp(v, "lbvh") == 0); }
     { const char* v = getenv("MCPT_LEAF_PAIRS"); s.fold_pairs = !(v && std::strcmp(v, "0") == 0); }
@@ -137,9 +138,9 @@ int alloc_scene(mcpt_ctx* c, int n) {
         carve(s.codes_obj, N); carve(s.codes_sorted, N); carve(s.iota, N); carve(s.leaf_face, N);
         carve(s.leaf_parent, N); carve(s.flags, N); carve(s.nodes, N); carve(s.tri, N);
         carve(s.shade, N); carve(s.root_box, 6); carve(s.qnodes, N); carve(s.qgrid, 1);
-        carve(s.qnodes4, N); carve(s.w4_queue, N); carve(s.w4_ctr, 4);
+        carve(s.qnodes4, N); carve(s.w4_queue, N); carve(s.w4_ctr, 8);
         carve(s.nodes2, N); carve(s.cl_lo[0], N); carve(s.cl_lo[1], N); carve(s.cl_hi[0], N); carve(s.cl_hi[1], N);
-        carve(s.ploc_nn, N); carve(s.ploc_flag, N); carve(s.ploc_scan, N);
+        carve(s.ploc_flag, N);
         carve_bytes(s.ploc_temp, s.ploc_temp_bytes); carve_bytes(s.ploc_state, 64); carve_bytes(s.cub_temp, s.cub_temp_bytes);
         if (pass == 0) { CU(c->scene_arena.reserve(used)); base = c->scene_arena.base; s.arena = base; }
     }
@@ -356,7 +357,12 @@ MCPT_API void mcpt_destroy(mcpt_ctx* c) {
 
 MCPT_API int mcpt_set_stream(mcpt_ctx* c, void* s) {
     if (!c) return fail_arg("mcpt_set_stream: null ctx");
-    c->stream = s ? (cudaStream_t)s : c->own_stream;
+    c->stream = (cudaStream_t)s;   // NULL is a stream too: CUDA's legacy default stream (what torch.cuda.current_stream() is by default)
+    return MCPT_OK;
+}
+MCPT_API int mcpt_use_own_stream(mcpt_ctx* c) {
+    if (!c) return fail_arg("mcpt_use_own_stream: null ctx");
+    c->stream = c->own_stream;
     return MCPT_OK;
 }
 MCPT_API int mcpt_set_seed(mcpt_ctx* c, uint64_t seed) {
@@ -492,19 +498,45 @@ MCPT_API int mcpt_get_scene_arrays(mcpt_ctx* c, double* pos, double* nrm, double
 MCPT_API int mcpt_build_bvh(mcpt_ctx* c, float* ms_out) {
     if (!c || !c->scene_loaded) return fail_arg("mcpt_build_bvh: upload a scene first");
     CU(cudaSetDevice(c->device));
+    c->sb.built = false;
+    c->sb.w4_resident_blocks = c->coop_blocks[0]; c->sb.ploc_resident_blocks = c->coop_blocks[1];   // occupancy queries, once per context
     CU(cudaEventRecord(c->ev0, c->stream));
     int launches = 0;
     const int e = lbvh_build(c->sb, c->stream, &launches);
     if (e) return fail_cuda((cudaError_t)e, "lbvh_build");
+    c->coop_blocks[0] = c->sb.w4_resident_blocks; c->coop_blocks[1] = c->sb.ploc_resident_blocks;
     CU(cudaEventRecord(c->ev1, c->stream));
     CU(cudaEventSynchronize(c->ev1));
+    // post-build verdicts (device flags): bad vertices; quality pass stalled; wide tree deeper than the traversal stack serves
+    unsigned w4[8] = {};
+    CU(cudaMemcpy(w4, c->sb.w4_ctr, sizeof(w4), cudaMemcpyDeviceToHost));
+    if (w4[5]) { c->sb.built = false; return fail_arg("mcpt_build_bvh: a vertex coordinate is not finite or beyond +-1e18"); }
+    bool fallback = false;
+    if (!c->sb.walk_is_radix) {
+        cudaError_t pe = cudaSuccess;
+        if (!ploc_ok(c->sb, &pe)) { if (pe != cudaSuccess) return fail_cuda(pe, "ploc state"); fallback = true; }
+    }
+#if MCPT_WIDE
+    auto wide_bad = [&]() { return w4[3] || !w4[2]; };
+    auto too_deep = [&]() { return w4[4] > MCPT_MAX_WIDE_LEVELS; };
+    if (!fallback && !c->sb.walk_is_radix && (wide_bad() || too_deep())) fallback = true;
+#endif
+    if (fallback) {   // walk the radix tree instead (its depth is bounded by the key length)
+        const int fe = lbvh_fallback_to_radix(c->sb, c->stream, &launches);
+        if (fe) return fail_cuda((cudaError_t)fe, "lbvh_fallback_to_radix");
+        CU(cudaEventRecord(c->ev1, c->stream));
+        CU(cudaEventSynchronize(c->ev1));
+        CU(cudaMemcpy(w4, c->sb.w4_ctr, sizeof(w4), cudaMemcpyDeviceToHost));
+    }
     CU(cudaEventElapsedTime(&c->last_build_ms, c->ev0, c->ev1));
     if (ms_out) *ms_out = c->last_build_ms;
     c->last_build_launches = launches;
 #if MCPT_WIDE
-    unsigned w4[4] = {0, 0, 0, 0};
-    CU(cudaMemcpy(w4, c->sb.w4_ctr, sizeof(w4), cudaMemcpyDeviceToHost));
-    if (w4[3] || !w4[2]) return fail_cuda(cudaErrorLaunchTimeout, "wide_build: the breadth-first collapse did not finish");
+    if (wide_bad()) { c->sb.built = false; return fail_cuda(cudaErrorLaunchTimeout, "wide_build: the breadth-first collapse did not finish"); }
+    if (too_deep()) {
+        c->sb.built = false;
+        return fail_arg("mcpt_build_bvh: the tree is deeper than the traversal stack serves (more than 21 wide levels): degenerate geometry");
+    }
 #endif
     return MCPT_OK;
 }
@@ -548,7 +580,7 @@ MCPT_API int mcpt_get_traversal_tree(mcpt_ctx* c, float* nodes16, int32_t* root)
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
     const int n_nodes = c->sb.n_faces > 1 ? c->sb.n_faces - 1 : 1;
-    const BvhNode* src = (c->sb.use_ploc && c->sb.n_faces >= 2) ? c->sb.nodes2 : c->sb.nodes;
+    const BvhNode* src = c->sb.walk_is_radix ? c->sb.nodes : c->sb.nodes2;
     if (nodes16) CU(cudaMemcpy(nodes16, src, sizeof(BvhNode) * (size_t)n_nodes, cudaMemcpyDeviceToHost));
     if (root) *root = c->sb.root;
     return MCPT_OK;

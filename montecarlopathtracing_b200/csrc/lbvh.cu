@@ -27,11 +27,18 @@ __device__ __forceinline__ unsigned quantize_axis(float x) {
 }
 // One thread per face.  The centroid is formed in FP64 from the FP64 vertices and only then narrowed
 // to FP32, exactly like the call at MTPC/sceneManagement.cpp:176-179.
+// Also zeroes the refit's arrival counters, and raises *bad when a coordinate is not finite or beyond +-1e18 (the build's FP32 box
+// areas would overflow or turn NaN; mcpt_build_bvh then fails with MCPT_ERR_ARG instead of building a tree nothing can hit).
 __global__ void __launch_bounds__(256) morton_kernel(const double* __restrict__ pos, int n, uint32_t* __restrict__ codes,
-                                                     int* __restrict__ iota) {
+                                                     int* __restrict__ iota, unsigned* __restrict__ flags, unsigned* __restrict__ bad) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    if (i < n - 1) flags[i] = 0u;
     const double* p = pos + 9 * (size_t)i;
+    bool ok = true;
+#pragma unroll
+    for (int a = 0; a < 9; a++) ok = ok && (fabs(p[a]) <= 1.0e18);   // false for NaN and inf
+    if (!ok) *bad = 1u;
     const double cx = __ddiv_rn(__dadd_rn(__dadd_rn(p[0], p[3]), p[6]), 3.0);
     const double cy = __ddiv_rn(__dadd_rn(__dadd_rn(p[1], p[4]), p[7]), 3.0);
     const double cz = __ddiv_rn(__dadd_rn(__dadd_rn(p[2], p[5]), p[8]), 3.0);
@@ -104,9 +111,10 @@ __global__ void __launch_bounds__(256) emit_refit_kernel(int n, const double* __
                                                          const int* __restrict__ leaf_face, const int* __restrict__ leaf_parent,
                                                          BvhNode* nodes, unsigned* flags, TriGeom* __restrict__ tri,
                                                          TriShade* __restrict__ shade, float* __restrict__ root_box,
-                                                         float4* __restrict__ cl_lo, float4* __restrict__ cl_hi) {
+                                                         float4* __restrict__ cl_lo, float4* __restrict__ cl_hi, int* __restrict__ w4_queue) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
+    w4_queue[k] = -1;   // wide.cu's W4_EMPTY: the collapse's queue is prepared on the way (saves a memset launch)
     const int f = leaf_face[k];
     const double* p = pos + 9 * (size_t)f;
     float v[9];
@@ -149,8 +157,11 @@ __global__ void __launch_bounds__(256) emit_refit_kernel(int n, const double* __
         const int* c = reinterpret_cast<const int*>(&node->q[3]);
         const int slot = (c[0] == child) ? 0 : 1;
         store_child_box(node, slot, b);
-        __threadfence();
-        if (atomicAdd(&flags[parent], 1u) == 0u) return;  // sibling subtree not finished yet
+        // release our box / acquire the sibling's with ONE acq_rel atomic at GPU scope instead of __threadfence() (a
+        // sequentially-consistent MEMBAR.SC, the kernel's top stall in round 1's ncu capture) + a relaxed atomic
+        unsigned arrived;
+        asm volatile("atom.add.acq_rel.gpu.u32 %0, [%1], 1;" : "=r"(arrived) : "l"(&flags[parent]) : "memory");
+        if (arrived == 0u) return;  // sibling subtree not finished yet
         const Box3 o = load_child_box(node, slot ^ 1);
 #pragma unroll
         for (int a = 0; a < 3; a++) { b.lo[a] = fminf(b.lo[a], o.lo[a]); b.hi[a] = fmaxf(b.hi[a], o.hi[a]); }
@@ -197,32 +208,52 @@ int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches) {
     const int n = sb.n_faces;
     const int tpb = 256;
     int nl = 0;
-    morton_kernel<<<(n + tpb - 1) / tpb, tpb, 0, stream>>>(sb.pos, n, sb.codes_obj, sb.iota); nl++;
+    cudaError_t e = cudaMemsetAsync(sb.w4_ctr, 0, 8 * sizeof(unsigned), stream);   // [5] = K1's bad-vertex flag
+    if (e != cudaSuccess) return (int)e;
+    morton_kernel<<<(n + tpb - 1) / tpb, tpb, 0, stream>>>(sb.pos, n, sb.codes_obj, sb.iota, sb.flags, sb.w4_ctr + 5); nl++;
     // stable LSD radix sort of (code, face index), 30 key bits: ties keep face-index order
-    cudaError_t e = cub::DeviceRadixSort::SortPairs(sb.cub_temp, sb.cub_temp_bytes, sb.codes_obj, sb.codes_sorted, sb.iota,
-                                                    sb.leaf_face, n, 0, 30, stream);
+    e = cub::DeviceRadixSort::SortPairs(sb.cub_temp, sb.cub_temp_bytes, sb.codes_obj, sb.codes_sorted, sb.iota,
+                                        sb.leaf_face, n, 0, 30, stream);
     if (e != cudaSuccess) return (int)e;
     nl += 4;
-    if (n > 1) {
-        cudaMemsetAsync(sb.flags, 0, sizeof(unsigned) * (size_t)(n - 1), stream);
-        radix_tree_kernel<<<(n - 1 + tpb - 1) / tpb, tpb, 0, stream>>>(sb.codes_sorted, n, sb.nodes, sb.leaf_parent); nl++;
-    }
+    if (n > 1) { radix_tree_kernel<<<(n - 1 + tpb - 1) / tpb, tpb, 0, stream>>>(sb.codes_sorted, n, sb.nodes, sb.leaf_parent); nl++; }
     emit_refit_kernel<<<(n + tpb - 1) / tpb, tpb, 0, stream>>>(n, sb.pos, sb.nrm, sb.uv, sb.mat_id, sb.leaf_face, sb.leaf_parent,
-                                                               sb.nodes, sb.flags, sb.tri, sb.shade, sb.root_box, sb.cl_lo[0], sb.cl_hi[0]); nl++;
-    const int n_nodes = n > 1 ? n - 1 : 1;
+                                                               sb.nodes, sb.flags, sb.tri, sb.shade, sb.root_box, sb.cl_lo[0], sb.cl_hi[0], sb.w4_queue); nl++;
     const BvhNode* walk = sb.nodes;
-    sb.root = 0;
+    sb.root = 0; sb.walk_is_radix = true;
+    bool w4_prepared = false;
     if (sb.use_ploc && n >= 2) {
-        const int pe = ploc_build(sb, stream, &nl);
+        const int pe = ploc_build(sb, stream, &nl, MCPT_WIDE != 0);
         if (pe) return pe;
-        walk = sb.nodes2; sb.root = n - 2;
+        walk = sb.nodes2; sb.root = n - 2; sb.walk_is_radix = false;
+        w4_prepared = MCPT_WIDE != 0;
     }
-    quantize_nodes_kernel<<<(n_nodes + tpb - 1) / tpb, tpb, 0, stream>>>(n_nodes, walk, sb.root_box, sb.qnodes, sb.qgrid, sb.fold_pairs && n > 2); nl++;
 #if MCPT_WIDE
-    { const int we = wide_build(sb, walk, sb.root, stream, &nl); if (we) return we; }
+    { const int we = wide_build(sb, walk, sb.root, stream, &nl, w4_prepared); if (we) return we; }
+#else
+    (void)w4_prepared;
+    const int n_nodes = n > 1 ? n - 1 : 1;
+    quantize_nodes_kernel<<<(n_nodes + tpb - 1) / tpb, tpb, 0, stream>>>(n_nodes, walk, sb.root_box, sb.qnodes, sb.qgrid, sb.fold_pairs && n > 2); nl++;
 #endif
     if (launches) *launches = nl;
     sb.built = true;
+    return (int)cudaGetLastError();
+}
+
+// The radix tree as the traversal tree (the quality pass stalled, or its tree is too deep for the traversal stack).  K3 left
+// the scene box in root_box (the radix root's box; the PLOC finish writes the same union), so only the collapse is redone.
+int lbvh_fallback_to_radix(SceneBuffers& sb, cudaStream_t stream, int* launches) {
+    const int n = sb.n_faces;
+    int nl = 0;
+    sb.root = 0; sb.walk_is_radix = true;
+#if MCPT_WIDE
+    { const int we = wide_build(sb, sb.nodes, 0, stream, &nl, false); if (we) return we; }
+#else
+    const int n_nodes = n > 1 ? n - 1 : 1;
+    quantize_nodes_kernel<<<(n_nodes + 255) / 256, 256, 0, stream>>>(n_nodes, sb.nodes, sb.root_box, sb.qnodes, sb.qgrid, sb.fold_pairs && n > 2); nl++;
+#endif
+    (void)n;
+    if (launches) *launches += nl;
     return (int)cudaGetLastError();
 }
 

@@ -23,15 +23,19 @@ struct SceneBuffers {
     QGrid* qgrid = nullptr;
     QNode4* qnodes4 = nullptr;         // 4-wide traversal nodes (wide.cu), breadth-first, root = 0
     int* w4_queue = nullptr;           // wide node -> the binary node it is rooted at
-    unsigned* w4_ctr = nullptr;        // queue tail (= number of wide nodes), processed, finished, error
+    unsigned* w4_ctr = nullptr;        // queue tail (= number of wide nodes), processed, finished, error, internal levels
+    int w4_resident_blocks = 0;        // co-resident CTAs of wide_collapse_kernel on this context's device (occupancy query)
+    unsigned* build_err = nullptr;     // device flag set by K1 when a vertex is not finite or beyond +-1e18 (checked by mcpt_build_bvh)
     void* cub_temp = nullptr; size_t cub_temp_bytes = 0;
     // quality pass (ploc.cu): the tree traversal walks
     bool use_ploc = true;              // MCPT_BVH=lbvh keeps the radix tree for traversal (A/B measurements)
     bool fold_pairs = true;            // MCPT_LEAF_PAIRS=0 keeps one triangle per leaf reference (A/B measurements)
     BvhNode* nodes2 = nullptr;         // PLOC tree, n-1 nodes, root = n-2
     float4* cl_lo[2] = {nullptr, nullptr}; float4* cl_hi[2] = {nullptr, nullptr};   // cluster boxes (+ref in lo.w), ping-pong
-    int* ploc_nn = nullptr; unsigned long long* ploc_flag = nullptr; unsigned long long* ploc_scan = nullptr;
-    void* ploc_temp = nullptr; size_t ploc_temp_bytes = 0; void* ploc_state = nullptr;
+    unsigned char* ploc_flag = nullptr;   // one byte per cluster: survives | merges-as-left << 1 | (partner offset + RADIUS) << 2
+    void* ploc_temp = nullptr; size_t ploc_temp_bytes = 0; void* ploc_state = nullptr;   // per-CTA counts; PlocState
+    int ploc_resident_blocks = 0;      // co-resident CTAs of ploc_rounds_kernel on this context's device
+    bool walk_is_radix = false;        // the traversal tree is the radix tree (MCPT_BVH=lbvh, or the quality pass fell back)
     int root = 0;                      // root of the traversal tree (0: radix tree, n-2: PLOC tree)
     void* arena = nullptr;             // every pointer above is carved from this one allocation (api.cu alloc_scene)
     bool built = false;
@@ -42,11 +46,18 @@ size_t lbvh_sort_temp_bytes(int n);
 // K1 Morton -> CUB radix sort -> K2 radix tree -> K3 leaf emit + atomic bottom-up refit -> K4 node quantisation.
 // Returns a cudaError_t as int; all work is enqueued on `stream`.
 int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches);
+// Redo the wide collapse over the radix tree (quality pass stalled / too deep); enqueued on `stream`.
+int lbvh_fallback_to_radix(SceneBuffers& sb, cudaStream_t stream, int* launches);
 // K4a (ploc.cu): parallel locally-ordered clustering over the Morton-ordered leaf boxes -> sb.nodes2.
-size_t ploc_scan_temp_bytes(int n);
-int ploc_build(SceneBuffers& sb, cudaStream_t stream, int* launches);
+size_t ploc_scratch_bytes(int n);
+int ploc_build(SceneBuffers& sb, cudaStream_t stream, int* launches, bool init_w4);
+// After the stream has been synchronised: did the quality pass finish (false: stalled, sb.nodes2 is unusable)?
+bool ploc_ok(const SceneBuffers& sb, cudaError_t* err);
 
 // K4b (wide.cu): collapse the binary traversal tree `walk` (root `root2`) into sb.qnodes4.
-int wide_build(SceneBuffers& sb, const BvhNode* walk, int root2, cudaStream_t stream, int* launches);
+// prepared: the queue is already filled with W4_EMPTY and the counters are reset (K3 and the PLOC finish kernel do that on the way).
+int wide_build(SceneBuffers& sb, const BvhNode* walk, int root2, cudaStream_t stream, int* launches, bool prepared);
+// Internal levels of the wide tree a traversal stack of MCPT_STACK_SIZE entries can serve (3 pushes per level + the sentinel).
+#define MCPT_MAX_WIDE_LEVELS 21
 
 }  // namespace mcpt

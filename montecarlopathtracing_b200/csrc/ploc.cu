@@ -5,17 +5,19 @@
 // is 99.9 % of a render.  This pass builds the tree that traversal actually walks by parallel locally-ordered
 // clustering (Meister & Bittner 2018) over the SAME Morton-sorted leaf sequence the radix tree is built on:
 //   repeat until one cluster is left:
-//     nn      every cluster looks at its RADIUS neighbours on either side in the (Morton-ordered) cluster array and picks
-//             the one whose merged box has the smallest surface area (ties: lowest index, which guarantees a mutual pair);
-//     flags   mutually-nearest pairs (i < j) become a new internal node at i, j dies;
-//     scan    one exclusive scan of packed (survivors, merges) gives every survivor its new position (order preserved)
-//             and every merge its node index (so the tree does not depend on scheduling);
-//     scatter writes the new nodes (64-B BvhNode: both child boxes + child references) and the compacted cluster array.
-// Once <= 1024 clusters remain a single CTA finishes the job in shared memory.  Node boxes are exact unions of the
+//     every cluster looks at its RADIUS neighbours on either side in the (Morton-ordered) cluster array and picks the one
+//     whose merged box has the smallest surface area (ties: the buddy i^1, then the lowest index — a mutual pair always exists);
+//     mutually-nearest pairs (i < j) become a new internal node at i, j dies;
+//     an order-preserving compaction gives every survivor its new position and every merge its node index in array order
+//     (so the tree does not depend on scheduling) and writes the new nodes (64-B BvhNode: both child boxes + references).
+// The rounds above 1024 clusters run in ONE cooperatively launched persistent kernel (two grid barriers per round), then a
+// single CTA finishes the job in shared memory.  Node boxes are exact unions of the
 // padded FP32 leaf boxes of K3, so no refit is needed.  Leaf order, leaf indices and the Morton codes are untouched.
+#include <cooperative_groups.h>
 #include <cub/block/block_scan.cuh>
-#include <cub/device/device_scan.cuh>
 #include "lbvh.h"
+
+namespace cg = cooperative_groups;
 
 namespace mcpt {
 
@@ -24,13 +26,32 @@ namespace mcpt {
 #endif
 #define PLOC_TPB 256
 #define PLOC_FINISH 1024
-
-struct PlocState { int m; int node_base; };   // clusters alive, internal nodes created so far
+#define PLOC_MAX_ITERS 4096
 
 __device__ __forceinline__ float merged_area(const float4 alo, const float4 ahi, const float4 blo, const float4 bhi) {
     const float dx = fmaxf(ahi.x, bhi.x) - fminf(alo.x, blo.x), dy = fmaxf(ahi.y, bhi.y) - fminf(alo.y, blo.y),
                 dz = fmaxf(ahi.z, bhi.z) - fminf(alo.z, blo.z);
     return __fadd_rn(__fadd_rn(__fmul_rn(dx, dy), __fmul_rn(dy, dz)), __fmul_rn(dz, dx));   // symmetric in (a, b), no FMA
+}
+
+// Nearest neighbour of cluster i among i-RADIUS .. i+RADIUS (global indices, 0 <= j < m): smallest merged area; among equal
+// areas the buddy i^1 first, then the lowest index.  A mutual pair always exists: take the globally smallest area A*; if some
+// buddy pair (i, i^1) reaches A*, both pick each other; otherwise the preference never applies at A* and the lowest-index
+// cluster taking part in an A* pair and its lowest-index A* partner pick each other.  The buddy rule is what keeps
+// tie-heavy input (regular grids, duplicated triangles: every area equal) at n/2 merges per round instead of ONE.
+// slo/shi hold the boxes of clusters base .. ; `at` = index of cluster i in them.
+__device__ __forceinline__ int ploc_nearest(const float4* __restrict__ slo, const float4* __restrict__ shi, const int at, const int i, const int m) {
+    const float4 alo = slo[at], ahi = shi[at];
+    float best = 3.0e38f; int bj = -1;
+#pragma unroll
+    for (int off = -PLOC_RADIUS; off <= PLOC_RADIUS; off++) {
+        if (off == 0) continue;
+        const int j = i + off;
+        if (j < 0 || j >= m) continue;
+        const float a = merged_area(alo, ahi, slo[at + off], shi[at + off]);
+        if (a < best || (a == best && j == (i ^ 1))) { best = a; bj = j; }   // strict <: ties keep the lowest index, but for the buddy
+    }
+    return bj;
 }
 
 // lo.w carries the cluster's reference (internal node index >= 0, leaf ~k < 0) as int bits.
@@ -43,101 +64,148 @@ __device__ __forceinline__ void write_node(BvhNode* nodes, int id, const float4 
     nodes[id] = nd;
 }
 
-// ---- global-memory iteration -------------------------------------------------------------------------------
-__global__ void __launch_bounds__(PLOC_TPB) ploc_nn_kernel(const PlocState* __restrict__ st, const float4* __restrict__ lo,
-                                                           const float4* __restrict__ hi, int* __restrict__ nn) {
-    __shared__ float4 slo[PLOC_TPB + 2 * PLOC_RADIUS], shi[PLOC_TPB + 2 * PLOC_RADIUS];
-    const int m = st->m;
-    for (int base = blockIdx.x * PLOC_TPB; base < m; base += gridDim.x * PLOC_TPB) {
-        __syncthreads();
-        for (int t = threadIdx.x; t < PLOC_TPB + 2 * PLOC_RADIUS; t += PLOC_TPB) {
-            const int g = base - PLOC_RADIUS + t;
-            if (g >= 0 && g < m) { slo[t] = lo[g]; shi[t] = hi[g]; }
-        }
-        __syncthreads();
-        const int i = base + threadIdx.x;
-        if (i < m) {
-            const int c = threadIdx.x + PLOC_RADIUS;
-            const float4 alo = slo[c], ahi = shi[c];
-            float best = 3.0e38f; int bj = -1;
-#pragma unroll
-            for (int off = -PLOC_RADIUS; off <= PLOC_RADIUS; off++) {
-                if (off == 0) continue;
-                const int j = i + off;
-                if (j < 0 || j >= m) continue;
-                const float a = merged_area(alo, ahi, slo[c + off], shi[c + off]);
-                if (a < best) { best = a; bj = j; }   // strict <: ties keep the lowest index
+// ---- the rounds above PLOC_FINISH clusters: ONE persistent, cooperatively launched kernel -----------------------------
+// (Round 1 ran every round as four kernels + a CUB scan and synchronised with the host every fourth round to read the
+// cluster count: ~60 launches and three host round trips for cornell-box, 0.36 of the build's 0.60 ms.)  Every CTA owns a
+// contiguous range of the cluster array, so the order-preserving compaction needs only per-CTA counts:
+//   phase 1  per cluster: nearest neighbour j, and j's own nearest neighbour recomputed from the same shared-memory tile
+//            (halo 2 x RADIUS) — the mutual test needs no second pass; one flag byte per cluster (survives | merges-as-left |
+//            offset of j), per-CTA counts of survivors and merges                                     -> grid.sync
+//   phase 2  every CTA sums the counts of the CTAs before it (and all of them: the next round's cluster count, identical
+//            in every CTA, no global state), scans its flags tile by tile and scatters survivors / writes the new nodes
+//            in array order — so node numbering does not depend on scheduling                          -> grid.sync
+#define PLOC_HALO (2 * PLOC_RADIUS)
+struct PlocState { int m; int node_base; int error; int rounds; };   // clusters alive, internal nodes created, stalled, rounds run
+
+__global__ void __launch_bounds__(PLOC_TPB) ploc_rounds_kernel(PlocState* st, float4* lo0, float4* hi0, float4* lo1, float4* hi1,
+                                                               unsigned char* __restrict__ flagb, uint2* blockcnt, BvhNode* __restrict__ nodes,
+                                                               const int n) {
+    cg::grid_group grid = cg::this_grid();
+    typedef cub::BlockScan<unsigned long long, PLOC_TPB> Scan;
+    __shared__ typename Scan::TempStorage temp;
+    __shared__ float4 slo[PLOC_TPB + 2 * PLOC_HALO], shi[PLOC_TPB + 2 * PLOC_HALO];
+    __shared__ unsigned s_red[2][PLOC_TPB / 32];
+    __shared__ unsigned long long s_pre[2];
+    const int G = gridDim.x, b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int m = n, node_base = 0, rounds = 0, error = 0;
+    float4 *lo = lo0, *hi = hi0, *lo_out = lo1, *hi_out = hi1;
+    while (m > PLOC_FINISH) {
+        const int per = ((m + G - 1) / G + PLOC_TPB - 1) / PLOC_TPB * PLOC_TPB;
+        const int r0 = min(b * per, m), r1 = min(r0 + per, m);
+        // ---- phase 1 ----
+        unsigned n_surv = 0, n_left = 0;
+        for (int base = r0; base < r1; base += PLOC_TPB) {
+            __syncthreads();
+            for (int t = tid; t < PLOC_TPB + 2 * PLOC_HALO; t += PLOC_TPB) {
+                const int g = base - PLOC_HALO + t;
+                if (g >= 0 && g < m) { slo[t] = lo[g]; shi[t] = hi[g]; }
             }
-            nn[i] = bj;
+            __syncthreads();
+            const int i = base + tid;
+            bool survive = false, left = false;
+            if (i < r1) {
+                const int j = ploc_nearest(slo, shi, tid + PLOC_HALO, i, m);
+                const bool mutual = j >= 0 && ploc_nearest(slo, shi, j - base + PLOC_HALO, j, m) == i;
+                survive = !(mutual && i > j); left = mutual && i < j;
+                flagb[i] = (unsigned char)((unsigned)survive | ((unsigned)left << 1) | ((unsigned)(j - i + PLOC_RADIUS) << 2));
+            }
+            const unsigned ms = __ballot_sync(0xffffffffu, survive), ml = __ballot_sync(0xffffffffu, left);
+            if (lane == 0) { n_surv += __popc(ms); n_left += __popc(ml); }
         }
-    }
-}
-
-// flag[i] = (survives << 32) | merges-as-left; zero beyond m (the scan runs over a host-side upper bound of m)
-__global__ void __launch_bounds__(PLOC_TPB) ploc_flags_kernel(const PlocState* __restrict__ st, const int* __restrict__ nn,
-                                                              unsigned long long* __restrict__ flag, int m_bound) {
-    const int m = st->m;
-    for (int i = blockIdx.x * PLOC_TPB + threadIdx.x; i < m_bound; i += gridDim.x * PLOC_TPB) {
-        unsigned long long f = 0ull;
-        if (i < m) {
-            const int j = nn[i];
-            const bool mutual = j >= 0 && nn[j] == i;
-            f = ((unsigned long long)(!(mutual && i > j)) << 32) | (unsigned long long)(mutual && i < j);
+        if (lane == 0) { s_red[0][warp] = n_surv; s_red[1][warp] = n_left; }
+        __syncthreads();
+        if (tid == 0) {
+            unsigned a = 0, c = 0;
+            for (int w = 0; w < PLOC_TPB / 32; w++) { a += s_red[0][w]; c += s_red[1][w]; }
+            blockcnt[b] = make_uint2(a, c);
         }
-        flag[i] = f;
-    }
-}
-
-__global__ void __launch_bounds__(PLOC_TPB) ploc_scatter_kernel(const PlocState* __restrict__ st, PlocState* __restrict__ st_next,
-                                                                const int* __restrict__ nn, const unsigned long long* __restrict__ flag,
-                                                                const unsigned long long* __restrict__ scan, const float4* __restrict__ lo,
-                                                                const float4* __restrict__ hi, float4* __restrict__ lo_out,
-                                                                float4* __restrict__ hi_out, BvhNode* __restrict__ nodes) {
-    const int m = st->m, node_base = st->node_base;
-    for (int i = blockIdx.x * PLOC_TPB + threadIdx.x; i < m; i += gridDim.x * PLOC_TPB) {
-        const unsigned long long f = flag[i], s = scan[i];
-        const bool survive = (f >> 32) != 0ull, left = (f & 1ull) != 0ull;
-        if (i == m - 1) { st_next->m = (int)(s >> 32) + (int)survive; st_next->node_base = node_base + (int)(s & 0xffffffffull) + (int)left; }
-        if (!survive) continue;
-        const int pos = (int)(s >> 32);
-        float4 alo = lo[i], ahi = hi[i];
-        if (left) {
-            const int j = nn[i];
-            const float4 blo = lo[j], bhi = hi[j];
-            const int id = node_base + (int)(s & 0xffffffffull);
-            write_node(nodes, id, alo, ahi, blo, bhi);
-            alo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), __int_as_float(id));
-            ahi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.0f);
+        grid.sync();
+        // ---- phase 2 ----
+        unsigned long long before = 0ull, total = 0ull;   // packed (survivors << 32 | merges)
+        for (int k = tid; k < G; k += PLOC_TPB) {
+            const uint2 c = __ldcg(&blockcnt[k]);
+            const unsigned long long v = ((unsigned long long)c.x << 32) | c.y;
+            total += v; if (k < b) before += v;
         }
-        lo_out[pos] = alo; hi_out[pos] = ahi;
+        before = __reduce_add_sync(0xffffffffu, (unsigned)(before >> 32)) * (1ull << 32) + __reduce_add_sync(0xffffffffu, (unsigned)before);
+        total = __reduce_add_sync(0xffffffffu, (unsigned)(total >> 32)) * (1ull << 32) + __reduce_add_sync(0xffffffffu, (unsigned)total);
+        __syncthreads();   // s_red free again
+        if (lane == 0) { s_red[0][warp] = (unsigned)(before >> 32); s_red[1][warp] = (unsigned)before; }
+        __syncthreads();
+        if (tid == 0) {
+            unsigned a = 0, c = 0;
+            for (int w = 0; w < PLOC_TPB / 32; w++) { a += s_red[0][w]; c += s_red[1][w]; }
+            s_pre[0] = ((unsigned long long)a << 32) | c;
+        }
+        __syncthreads();
+        if (lane == 0) { s_red[0][warp] = (unsigned)(total >> 32); s_red[1][warp] = (unsigned)total; }
+        unsigned long long running = s_pre[0];
+        __syncthreads();
+        if (tid == 0) {
+            unsigned a = 0, c = 0;
+            for (int w = 0; w < PLOC_TPB / 32; w++) { a += s_red[0][w]; c += s_red[1][w]; }
+            s_pre[1] = ((unsigned long long)a << 32) | c;
+        }
+        __syncthreads();
+        total = s_pre[1];
+        for (int base = r0; base < r1; base += PLOC_TPB) {
+            const int i = base + tid;
+            unsigned f = 0u;
+            if (i < r1) f = flagb[i];
+            const bool survive = f & 1u, left = (f >> 1) & 1u;
+            unsigned long long s, tile_total;
+            Scan(temp).ExclusiveSum(((unsigned long long)survive << 32) | (unsigned long long)left, s, tile_total);
+            __syncthreads();   // temp reusable next tile
+            s += running; running += tile_total;
+            if (survive) {
+                const int pos = (int)(s >> 32);
+                float4 alo = lo[i], ahi = hi[i];
+                if (left) {
+                    const int j = i + (int)(f >> 2) - PLOC_RADIUS;
+                    const float4 blo = lo[j], bhi = hi[j];
+                    const int id = node_base + (int)(s & 0xffffffffull);
+                    write_node(nodes, id, alo, ahi, blo, bhi);
+                    alo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), __int_as_float(id));
+                    ahi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.0f);
+                }
+                lo_out[pos] = alo; hi_out[pos] = ahi;
+            }
+        }
+        const int m_next = (int)(total >> 32);
+        node_base += (int)(total & 0xffffffffull);
+        rounds++;
+        if (m_next >= m || rounds >= PLOC_MAX_ITERS) { error = 1; break; }   // no mutual pair (cannot happen on finite boxes) or runaway
+        m = m_next;
+        float4* t = lo; lo = lo_out; lo_out = t; t = hi; hi = hi_out; hi_out = t;
+        grid.sync();
     }
+    if (b == 0 && tid == 0) { st->m = m; st->node_base = node_base; st->error = error; st->rounds = rounds | ((lo == lo0 ? 0 : 1) << 30); }
 }
 
 // ---- single-CTA finish: <= PLOC_FINISH clusters, one per thread, everything in shared memory -----------------------
-__global__ void __launch_bounds__(PLOC_FINISH) ploc_finish_kernel(PlocState* st, const float4* __restrict__ lo, const float4* __restrict__ hi,
-                                                                  BvhNode* __restrict__ nodes, float* __restrict__ root_box) {
+__global__ void __launch_bounds__(PLOC_FINISH) ploc_finish_kernel(PlocState* st, const float4* __restrict__ lo0, const float4* __restrict__ hi0,
+                                                                  const float4* __restrict__ lo1, const float4* __restrict__ hi1,
+                                                                  BvhNode* __restrict__ nodes, float* __restrict__ root_box, unsigned* w4_ctr) {
     typedef cub::BlockScan<unsigned long long, PLOC_FINISH> Scan;
     __shared__ typename Scan::TempStorage temp;
-    __shared__ float4 slo[PLOC_FINISH], shi[PLOC_FINISH];
+    __shared__ float4 slo[PLOC_FINISH + 2 * PLOC_RADIUS], shi[PLOC_FINISH + 2 * PLOC_RADIUS];   // clusters at [RADIUS, RADIUS + m)
     __shared__ int snn[PLOC_FINISH];
     __shared__ int s_m, s_base;
     const int i = threadIdx.x;
+    if (i == 0 && w4_ctr) { w4_ctr[0] = 1u; w4_ctr[1] = 0u; w4_ctr[2] = 0u; w4_ctr[3] = 0u; w4_ctr[4] = 0u; }   // wide.cu's W4_* counters
     int m = st->m, node_base = st->node_base;
-    if (m > PLOC_FINISH) return;   // caller's contract
-    if (i < m) { slo[i] = lo[i]; shi[i] = hi[i]; }
+    if (m > PLOC_FINISH || st->error) return;   // the rounds kernel stalled: mcpt_build_bvh falls back to the radix tree
+    const bool second = (st->rounds >> 30) & 1;
+    const float4* lo = second ? lo1 : lo0; const float4* hi = second ? hi1 : hi0;
+    if (i < m) { slo[i + PLOC_RADIUS] = lo[i]; shi[i + PLOC_RADIUS] = hi[i]; }
     __syncthreads();
+    int rounds = 0;
     while (m > 1) {
         float4 alo = make_float4(0.f, 0.f, 0.f, 0.f), ahi = alo;
         int bj = -1;
         if (i < m) {
-            alo = slo[i]; ahi = shi[i];
-            float best = 3.0e38f;
-            for (int off = -PLOC_RADIUS; off <= PLOC_RADIUS; off++) {
-                const int j = i + off;
-                if (off == 0 || j < 0 || j >= m) continue;
-                const float a = merged_area(alo, ahi, slo[j], shi[j]);
-                if (a < best) { best = a; bj = j; }
-            }
+            alo = slo[i + PLOC_RADIUS]; ahi = shi[i + PLOC_RADIUS];
+            bj = ploc_nearest(slo, shi, i + PLOC_RADIUS, i, m);
             snn[i] = bj;
         }
         __syncthreads();
@@ -146,7 +214,7 @@ __global__ void __launch_bounds__(PLOC_FINISH) ploc_finish_kernel(PlocState* st,
         if (i < m) {
             const bool mutual = bj >= 0 && snn[bj] == i;
             survive = !(mutual && i > bj); left = mutual && i < bj;
-            if (left) { blo = slo[bj]; bhi = shi[bj]; }
+            if (left) { blo = slo[bj + PLOC_RADIUS]; bhi = shi[bj + PLOC_RADIUS]; }
         }
         const unsigned long long f = ((unsigned long long)survive << 32) | (unsigned long long)left;
         unsigned long long s, total;
@@ -160,60 +228,58 @@ __global__ void __launch_bounds__(PLOC_FINISH) ploc_finish_kernel(PlocState* st,
                 alo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), __int_as_float(id));
                 ahi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.0f);
             }
-            slo[pos] = alo; shi[pos] = ahi;
+            slo[pos + PLOC_RADIUS] = alo; shi[pos + PLOC_RADIUS] = ahi;
         }
         if (i == 0) { s_m = (int)(total >> 32); s_base = node_base + (int)(total & 0xffffffffull); }
         __syncthreads();
+        if (s_m >= m || ++rounds > PLOC_MAX_ITERS) { if (i == 0) st->error = 1; return; }
         m = s_m; node_base = s_base;
     }
     if (i == 0) {
         st->m = m; st->node_base = node_base;
-        root_box[0] = slo[0].x; root_box[1] = slo[0].y; root_box[2] = slo[0].z;
-        root_box[3] = shi[0].x; root_box[4] = shi[0].y; root_box[5] = shi[0].z;
+        root_box[0] = slo[PLOC_RADIUS].x; root_box[1] = slo[PLOC_RADIUS].y; root_box[2] = slo[PLOC_RADIUS].z;
+        root_box[3] = shi[PLOC_RADIUS].x; root_box[4] = shi[PLOC_RADIUS].y; root_box[5] = shi[PLOC_RADIUS].z;
     }
 }
 
 // ---- host ---------------------------------------------------------------------------------------------------
-size_t ploc_scan_temp_bytes(int n) {
-    size_t bytes = 0;
-    cub::DeviceScan::ExclusiveSum(nullptr, bytes, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, n);
-    return bytes;
+size_t ploc_scratch_bytes(int n) {   // per-CTA counts of the rounds kernel (<= 8 CTAs per SM on any device we accept)
+    (void)n;
+    return sizeof(uint2) * 4096;
 }
 
-// Builds sb.nodes2 (n-1 nodes, root = n-2) from the leaf boxes sb.cl_lo/cl_hi[0] written by K3.  Synchronises the
-// stream every few iterations to read the cluster count (the iteration count is data dependent).
-int ploc_build(SceneBuffers& sb, cudaStream_t stream, int* launches) {
+// Builds sb.nodes2 (n-1 nodes, root = n-2) from the leaf boxes sb.cl_lo/cl_hi[0] written by K3: two launches, no host
+// round trip.  A stall (st->error, checked by mcpt_build_bvh after the build) makes the caller fall back to the radix tree.
+// init_w4: let the finish kernel also reset wide.cu's counters (saves wide_build its own init launch).
+int ploc_build(SceneBuffers& sb, cudaStream_t stream, int* launches, bool init_w4) {
     const int n = sb.n_faces;
     if (n < 2) return 0;
     cudaError_t e;
-#define PL_CU(call) do { e = (call); if (e != cudaSuccess) return (int)e; } while (0)
-    const PlocState init = {n, 0};
-    PL_CU(cudaMemcpyAsync(sb.ploc_state, &init, sizeof(init), cudaMemcpyHostToDevice, stream));
-    int nl = 0, cur = 0, m_bound = n;
-    const int grid_cap = 148 * 8;
-    PlocState* st = (PlocState*)sb.ploc_state;   // st[0], st[1]: ping-pong with the cluster arrays
-    int which = 0;
-    while (m_bound > PLOC_FINISH) {
-        for (int rep = 0; rep < 4; rep++) {
-            const int blocks = min(grid_cap, (m_bound + PLOC_TPB - 1) / PLOC_TPB);
-            ploc_nn_kernel<<<blocks, PLOC_TPB, 0, stream>>>(st + which, sb.cl_lo[cur], sb.cl_hi[cur], sb.ploc_nn);
-            ploc_flags_kernel<<<blocks, PLOC_TPB, 0, stream>>>(st + which, sb.ploc_nn, sb.ploc_flag, m_bound);
-            size_t tb = sb.ploc_temp_bytes;
-            PL_CU(cub::DeviceScan::ExclusiveSum(sb.ploc_temp, tb, sb.ploc_flag, sb.ploc_scan, m_bound, stream));
-            ploc_scatter_kernel<<<blocks, PLOC_TPB, 0, stream>>>(st + which, st + (which ^ 1), sb.ploc_nn, sb.ploc_flag, sb.ploc_scan,
-                                                                 sb.cl_lo[cur], sb.cl_hi[cur], sb.cl_lo[cur ^ 1], sb.cl_hi[cur ^ 1], sb.nodes2);
-            nl += 5; cur ^= 1; which ^= 1;
-        }
-        PlocState h;
-        PL_CU(cudaMemcpyAsync(&h, st + which, sizeof(h), cudaMemcpyDeviceToHost, stream));
-        PL_CU(cudaStreamSynchronize(stream));
-        m_bound = h.m;
+    PlocState* st = (PlocState*)sb.ploc_state;
+    if (!sb.ploc_resident_blocks) {
+        int dev = 0, sms = 0, per_sm = 0, coop = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ploc_rounds_kernel, PLOC_TPB, 0);
+        if (e != cudaSuccess || sms <= 0 || per_sm <= 0 || !coop) return (int)(e != cudaSuccess ? e : cudaErrorInvalidConfiguration);
+        sb.ploc_resident_blocks = min(sms * per_sm, 4096);
     }
-    ploc_finish_kernel<<<1, PLOC_FINISH, 0, stream>>>(st + which, sb.cl_lo[cur], sb.cl_hi[cur], sb.nodes2, sb.root_box);
-    nl++;
-    if (launches) *launches += nl;
+    int blocks = min(sb.ploc_resident_blocks, (n + PLOC_TPB - 1) / PLOC_TPB);
+    float4 *lo0 = sb.cl_lo[0], *hi0 = sb.cl_hi[0], *lo1 = sb.cl_lo[1], *hi1 = sb.cl_hi[1];
+    unsigned char* flagb = (unsigned char*)sb.ploc_flag; uint2* blockcnt = (uint2*)sb.ploc_temp; BvhNode* nodes = sb.nodes2; int nn = n;
+    void* args[] = {(void*)&st, (void*)&lo0, (void*)&hi0, (void*)&lo1, (void*)&hi1, (void*)&flagb, (void*)&blockcnt, (void*)&nodes, (void*)&nn};
+    e = cudaLaunchCooperativeKernel((const void*)ploc_rounds_kernel, dim3(blocks), dim3(PLOC_TPB), args, 0, stream);
+    if (e != cudaSuccess) return (int)e;
+    ploc_finish_kernel<<<1, PLOC_FINISH, 0, stream>>>(st, lo0, hi0, lo1, hi1, sb.nodes2, sb.root_box, init_w4 ? sb.w4_ctr : nullptr);
+    if (launches) *launches += 2;
     return (int)cudaGetLastError();
-#undef PL_CU
+}
+
+bool ploc_ok(const SceneBuffers& sb, cudaError_t* err) {
+    PlocState h{};
+    *err = cudaMemcpy(&h, sb.ploc_state, sizeof(h), cudaMemcpyDeviceToHost);
+    return *err == cudaSuccess && h.error == 0 && h.m == 1;
 }
 
 }  // namespace mcpt

@@ -126,7 +126,8 @@ __device__ __forceinline__ void node4_step(const QNode4* __restrict__ nodes, int
     unsigned s2 = slab_key(k2, r, fx, fy, fz, best_t), s3 = slab_key(k3, r, fx, fy, fz, best_t);
     int r0 = (int)k0.w, r1 = (int)k1.w, r2 = (int)k2.w, r3 = (int)k3.w;
     pair_cswap(s0, r0, s1, r1); pair_cswap(s2, r2, s3, r3); pair_cswap(s0, r0, s2, r2); pair_cswap(s1, r1, s3, r3); pair_cswap(s1, r1, s2, r2);
-    sp = min(sp, MCPT_STACK_SIZE);   // the array has 4 spare entries: the three pushes below need no bounds test
+    // no bounds test: mcpt_build_bvh rejects (or rebuilds) a wide tree with more than MCPT_MAX_WIDE_LEVELS = 21 internal levels, and
+    // a depth-first walk holds at most the sentinel + 3 siblings per level above the current node: sp <= 1 + 3*20 before the pushes
     if (s3 != 0xFFFFFFFFu) { stack[sp] = r3; sp++; }
     if (s2 != 0xFFFFFFFFu) { stack[sp] = r2; sp++; }
     if (s1 != 0xFFFFFFFFu) { stack[sp] = r1; sp++; }

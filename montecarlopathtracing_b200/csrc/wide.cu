@@ -19,8 +19,11 @@
 
 namespace mcpt {
 
-enum { W4_TAIL = 0, W4_PROCESSED = 1, W4_FINISHED = 2, W4_ERROR = 3 };
+// W4_LEVELS = number of internal levels of the wide tree (root = level 1): what bounds the traversal stack (see wide_build)
+enum { W4_TAIL = 0, W4_PROCESSED = 1, W4_FINISHED = 2, W4_ERROR = 3, W4_LEVELS = 4 };
 #define W4_EMPTY (-1)
+// a queue entry = binary node id | (level of the wide node - 1) << 26; levels saturate at 31 (any tree that deep is rejected)
+#define W4_ID_MASK ((1 << MCPT_LEAF_BITS) - 1)
 #define W4_SPIN_LIMIT (1 << 20)
 
 struct W4Slot { float lo[3], hi[3]; int ref; };
@@ -38,15 +41,20 @@ __device__ __forceinline__ float w4_area(const W4Slot& s) {
 }
 
 __global__ void __launch_bounds__(256) wide_init_kernel(unsigned* ctr) {
-    ctr[W4_TAIL] = 1u; ctr[W4_PROCESSED] = 0u; ctr[W4_FINISHED] = 0u; ctr[W4_ERROR] = 0u;
+    ctr[W4_TAIL] = 1u; ctr[W4_PROCESSED] = 0u; ctr[W4_FINISHED] = 0u; ctr[W4_ERROR] = 0u; ctr[W4_LEVELS] = 0u;
 }
 
 __global__ void __launch_bounds__(256) wide_collapse_kernel(const BvhNode* __restrict__ nodes, const int root2, const int max_nodes,
                                                             const float* __restrict__ root_box, QNode4* __restrict__ out,
-                                                            int* queue, unsigned* ctr, const bool fold) {
+                                                            int* queue, unsigned* ctr, const bool fold, QGrid* __restrict__ qgrid) {
     const int stride = gridDim.x * blockDim.x, lane = threadIdx.x & 31;
     float o[3], cell[3], inv[3];
     quant_grid(root_box, o, cell, inv);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        qgrid->origin = make_float4(o[0], o[1], o[2], 0.0f);
+        qgrid->cell = make_float4(cell[0], cell[1], cell[2], 0.0f);
+    }
+    unsigned deepest = 0u;
     for (int t = blockIdx.x * blockDim.x + threadIdx.x;; t += stride) {   // warp-uniform trip count: the lanes of a warp advance together
         bool done = t >= max_nodes;
         bool fin = false;
@@ -60,7 +68,11 @@ __global__ void __launch_bounds__(256) wide_collapse_kernel(const BvhNode* __res
                 // (same-address atomics from every thread were the bound of the first version: 2.5 ms for 5 M triangles)
                 W4Slot s[4];
                 int cnt = 0, m = 0;
+                int level = 0;
                 if (ready) {
+                    level = t == 0 ? 0 : (id >> MCPT_LEAF_BITS);
+                    id &= W4_ID_MASK;
+                    deepest = max(deepest, (unsigned)level + 1u);
                     cnt = 2;
                     w4_children(nodes, id, fold, s[0], s[1]);
                     for (int step = 0; step < 2; step++) {
@@ -89,7 +101,7 @@ __global__ void __launch_bounds__(256) wide_collapse_kernel(const BvhNode* __res
                     for (int j = 0; j < 4; j++) {
                         if (j < cnt) {
                             int ref = s[j].ref;
-                            if (ref >= 0) { const int w = (int)base + k++; *(volatile int*)&queue[w] = ref; ref = w; }
+                            if (ref >= 0) { const int w = (int)base + k++; *(volatile int*)&queue[w] = ref | (min(level + 1, 31) << MCPT_LEAF_BITS); ref = w; }
                             q.c[j] = make_uint4(quant_lo(s[j].lo[0], o[0], inv[0]) | (quant_hi(s[j].hi[0], o[0], inv[0]) << 16),
                                                 quant_lo(s[j].lo[1], o[1], inv[1]) | (quant_hi(s[j].hi[1], o[1], inv[1]) << 16),
                                                 quant_lo(s[j].lo[2], o[2], inv[2]) | (quant_hi(s[j].hi[2], o[2], inv[2]) << 16), (unsigned)ref);
@@ -119,29 +131,40 @@ __global__ void __launch_bounds__(256) wide_collapse_kernel(const BvhNode* __res
         if (__any_sync(0xffffffffu, fin)) break;
         if (t - lane + stride >= max_nodes) break;   // no entries left for this warp
     }
+    deepest = __reduce_max_sync(0xffffffffu, deepest);
+    if (lane == 0 && deepest) atomicMax(&ctr[W4_LEVELS], deepest);
 }
 
-int wide_build(SceneBuffers& sb, const BvhNode* walk, int root2, cudaStream_t stream, int* launches) {
+int wide_build(SceneBuffers& sb, const BvhNode* walk, int root2, cudaStream_t stream, int* launches, bool prepared) {
     const int n = sb.n_faces;
     const int max_nodes = n > 1 ? n - 1 : 1;
-    cudaError_t e = cudaMemsetAsync(sb.w4_queue, 0xFF, sizeof(int) * (size_t)max_nodes, stream);
-    if (e != cudaSuccess) return (int)e;
-    wide_init_kernel<<<1, 1, 0, stream>>>(sb.w4_ctr);
-    // a fully RESIDENT grid (the no-deadlock argument needs every thread to be running): occupancy x SM count, asked of the runtime
-    static int resident_blocks = 0;
-    if (!resident_blocks) {
-        int dev = 0, sms = 0, per_sm = 0;
+    cudaError_t e = cudaSuccess;
+    if (!prepared) {
+        e = cudaMemsetAsync(sb.w4_queue, 0xFF, sizeof(int) * (size_t)max_nodes, stream);
+        if (e != cudaSuccess) return (int)e;
+        wide_init_kernel<<<1, 1, 0, stream>>>(sb.w4_ctr);
+        if (launches) *launches += 2;
+    }
+    // a fully RESIDENT grid (the no-deadlock argument needs every thread to be running): launched COOPERATIVELY, so the runtime
+    // refuses the launch instead of letting CTAs wait for SMs that another context or stream holds; the grid size comes from
+    // this device's occupancy (queried once per context: sb.w4_resident_blocks)
+    if (!sb.w4_resident_blocks) {
+        int dev = 0, sms = 0, per_sm = 0, coop = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wide_collapse_kernel, 256, 0);
-        if (e != cudaSuccess || sms <= 0 || per_sm <= 0) return (int)(e != cudaSuccess ? e : cudaErrorInvalidConfiguration);
-        resident_blocks = sms * per_sm;
+        if (e != cudaSuccess || sms <= 0 || per_sm <= 0 || !coop) return (int)(e != cudaSuccess ? e : cudaErrorInvalidConfiguration);
+        sb.w4_resident_blocks = sms * per_sm;
     }
     int blocks = (max_nodes + 255) / 256;
-    if (blocks > resident_blocks) blocks = resident_blocks;
-    wide_collapse_kernel<<<blocks, 256, 0, stream>>>(walk, root2, max_nodes, sb.root_box, sb.qnodes4, sb.w4_queue,
-                                                                      sb.w4_ctr, sb.fold_pairs && n > 2);
-    if (launches) *launches += 3;
+    if (blocks > sb.w4_resident_blocks) blocks = sb.w4_resident_blocks;
+    const float* root_box = sb.root_box; QNode4* out = sb.qnodes4; int* queue = sb.w4_queue; unsigned* ctr = sb.w4_ctr;
+    int mn = max_nodes, r2 = root2; bool fold = sb.fold_pairs && n > 2; QGrid* qgrid = sb.qgrid;
+    void* args[] = {(void*)&walk, (void*)&r2, (void*)&mn, (void*)&root_box, (void*)&out, (void*)&queue, (void*)&ctr, (void*)&fold, (void*)&qgrid};
+    e = cudaLaunchCooperativeKernel((const void*)wide_collapse_kernel, dim3(blocks), dim3(256), args, 0, stream);
+    if (e != cudaSuccess) return (int)e;
+    if (launches) *launches += 1;
     return (int)cudaGetLastError();
 }
 

@@ -292,3 +292,62 @@ def test_wide_tree_large_mesh(gpu_ctx):
             assert hits["tri"][i] >= 0 and abs(hits["t"][i] - t[best]) <= 1e-4 * t[best], (i, hits["tri"][i], best)
         else:
             assert abs(hits["t"][i] - t[best]) <= 1e-5 * max(t[best], 1e-3)
+
+
+def test_tie_heavy_input_builds_quickly_and_correctly(gpu_ctx):
+    """Identical and regularly spaced boxes make every merged area equal.  The quality pass breaks ties toward the buddy i^1 (then
+    the lowest index), so a round still merges ~half of the clusters instead of ONE (ploc.cu ploc_nearest); the tree must stay
+    shallow enough for the traversal stack and every triangle must be found."""
+    from montecarlopathtracing_b200.api import make_desc
+    n = 40000
+    base = np.array([[0.0, 0.0, 0.0], [0.01, 0.0, 0.0], [0.0, 0.01, 0.0]])
+    pos = np.repeat(base[None], n, axis=0)
+    pos[n // 2:, :, 0] += (np.arange(n - n // 2) * (1.0 / 64))[:, None] % 3.0      # second half: a regular strip, equal spacing
+    nrm = np.tile(np.array([0.0, 0.0, 1.0]), (n, 3, 1)); uv = np.zeros((n, 3, 2))
+    desc, keep = make_desc(pos, nrm, uv, np.zeros(n, np.int32), [{"kd": (0.5, 0.5, 0.5)}], [])
+    gpu_ctx.upload_scene(desc)
+    ms = gpu_ctx.build_bvh()
+    assert ms < 50.0, "tie-heavy build took %.1f ms" % ms
+    nodes, origin, cell = gpu_ctx.get_wide_tree()
+    tri_lo, tri_hi = pos.min(axis=1), pos.max(axis=1)
+    check_wide_tree(nodes, origin, cell, n, tri_lo, tri_hi)
+    # a ray into the stack of n/2 identical triangles: the reference's tie rule picks the lowest sorted leaf
+    hits = gpu_ctx.trace(np.array([[0.002, 0.002, 1.0, 1e-4, 1e-4, -1.0]], np.float32))
+    _, _, face_sorted = gpu_ctx.get_morton()
+    assert hits["leaf"][0] >= 0 and hits["tri"][0] == face_sorted[hits["leaf"][0]]
+    same_box = np.nonzero((tri_lo == tri_lo[hits["tri"][0]]).all(axis=1))[0]
+    leaf_of = np.empty(n, np.int64); leaf_of[face_sorted] = np.arange(n)
+    assert hits["leaf"][0] == leaf_of[same_box].min()
+
+
+def test_non_finite_vertices_are_rejected(gpu_ctx):
+    import montecarlopathtracing_b200 as M
+    for bad in (np.nan, np.inf, 1e19):
+        desc, keep = random_soup(64, seed=5)
+        keep[0][100] = bad
+        gpu_ctx.upload_scene(desc)
+        with pytest.raises(M.McptError, match="not finite"):
+            gpu_ctx.build_bvh()
+        with pytest.raises(M.McptError, match="build the BVH first"):
+            gpu_ctx.trace(np.zeros((1, 6), np.float32))
+    desc, _ = random_soup(64, seed=5)
+    gpu_ctx.upload_scene(desc); gpu_ctx.build_bvh()
+
+
+def test_build_succeeds_while_another_stream_keeps_the_gpu_busy(gpu_ctx, scenes):
+    """The collapse and the PLOC rounds need every CTA of their grid resident; they are launched cooperatively, so a busy
+    device delays them instead of deadlocking them (round 1 sized an ordinary launch from an occupancy query)."""
+    import torch
+    s = scenes["cornell-box"]
+    gpu_ctx.upload_scene(s)
+    gpu_ctx.build_bvh()
+    want = gpu_ctx.get_wide_tree()[0].shape[0]
+    side = torch.cuda.Stream()
+    a = torch.randn(8192, 8192, device="cuda")
+    with torch.cuda.stream(side):
+        for _ in range(40):
+            a = torch.tanh(a @ a * 1e-4)
+    for _ in range(5):
+        gpu_ctx.build_bvh()
+        assert gpu_ctx.get_wide_tree()[0].shape[0] == want
+    torch.cuda.synchronize()
