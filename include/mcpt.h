@@ -14,7 +14,7 @@
  * Conventions: every function returns 0 on success, a negative mcpt_status otherwise;
  * mcpt_last_error() gives the message (thread-local).  Handles are opaque.  The caller owns all
  * host buffers; the library owns device memory.  One context = one GPU; one host thread per
- * context.  Plain pointers and sizes only.  There is NO CPU fallback: without a usable CUDA device
+ * context (mcpt_multi drives several contexts from one call).  Plain pointers and sizes only.  There is NO CPU fallback: without a usable CUDA device
  * every compute call fails with MCPT_ERR_CUDA.
  */
 #ifndef MCPT_H
@@ -101,7 +101,7 @@ typedef struct mcpt_stats {
     float trace_ms;        /* wavefront mode: summed CUDA-event time of the wf_trace launches (the dominant kernel) */
     int32_t trace_launches;/* wavefront mode: number of wf_trace launches (= loop iterations) */
     int32_t build_launches;/* kernels launched by the last mcpt_build_bvh (ours + CUB's) */
-    int32_t reserved;
+    float exchange_ms;     /* multi-GPU renders, rank 0: CUDA-event time of the one exchange (grouped ncclSend/ncclRecv of the partial sums) */
 } mcpt_stats;
 
 enum { MCPT_MODE_MEGAKERNEL = 0, MCPT_MODE_WAVEFRONT = 1 };
@@ -226,6 +226,51 @@ MCPT_API int mcpt_render_chunks(mcpt_ctx* ctx, const mcpt_camera* cam, int width
  * the same association as inside mcpt_render, so 1/2/4/8-GPU images are bit-identical. */
 MCPT_API int mcpt_sum_partials(mcpt_ctx* ctx, const float* d_partials, int n, int64_t count, float scale,
                                float* d_out);
+
+/* Measurement aid (not on the product path): read bandwidth in GB/s of a 16-B-vector sweep that bypasses L1 over a working set
+ * of the given size, repeated `repeats` times — L2 -> SM bandwidth below the L2 size (126 MB on B200), HBM read bandwidth far
+ * above it.  bench.py reports the traversal kernels' algorithmic bytes against it. */
+MCPT_API int mcpt_measure_read_bandwidth(mcpt_ctx* ctx, int64_t working_set_bytes, int repeats, float* gbs_out);
+
+/* ---- multi-GPU: SPP split, scene replicated, ONE exchange, fixed-order sum ----------------------------
+ * The reference's only parallelism is the 8-thread OpenMP loop over one pixel's samples (MTPC/pathTracing.cpp:300-321).
+ * Rank r of R in {1,2,4,8} integrates chunks [r*C/R, (r+1)*C/R) of the MCPT_NUM_CHUNKS sample chunks; the R partial sums go to
+ * rank 0 in one grouped ncclSend/ncclRecv (straight into one R x count buffer) and are added by the same pairwise tree as inside
+ * mcpt_render, so the image does not depend on R, bit for bit.  NCCL (libnccl.so.2) is bound with dlopen on first use: a
+ * single-GPU user needs none. */
+
+/* (1) One process per GPU (torchrun, MPI).  Rank 0 makes the id, the launcher broadcasts its MCPT_COMM_ID_BYTES bytes, every
+ * rank joins with its own context (ncclCommInitRank).  mcpt_render_dist is COLLECTIVE: every rank calls it with the same
+ * arguments after uploading / building the same scene; the mean image arrives in rank 0's HOST buffer rgb_out (ignored on the
+ * other ranks; NULL on rank 0 leaves it on the device, see mcpt_device_image).  stats: this rank's samples and rays; rank 0
+ * also gets exchange_ms. */
+#define MCPT_COMM_ID_BYTES 128
+MCPT_API int mcpt_comm_unique_id(char id_out[MCPT_COMM_ID_BYTES]);
+MCPT_API int mcpt_comm_init(mcpt_ctx* ctx, int world, int rank, const char id[MCPT_COMM_ID_BYTES]);
+MCPT_API int mcpt_comm_destroy(mcpt_ctx* ctx);
+MCPT_API int mcpt_render_dist(mcpt_ctx* ctx, const mcpt_camera* cam, int width, int height, int spp, int mode, int flags,
+                              float* rgb_out, mcpt_stats* stats);
+/* DEVICE pointer of the last mean image mcpt_render / mcpt_render_png / mcpt_render_dist (rank 0) left on this context. */
+MCPT_API const float* mcpt_device_image(mcpt_ctx* ctx);
+
+/* (2) One process driving n_dev GPUs (what the C++ host does: render_scene, mcpt_cli --gpus): ncclCommInitAll, one host thread
+ * per GPU inside the calls.  devices == NULL means 0 .. n_dev-1.  Same image as one GPU, bit for bit.  stats: samples and rays
+ * summed over the GPUs, times = the slowest GPU's. */
+typedef struct mcpt_multi mcpt_multi;
+MCPT_API int mcpt_multi_create(const int* devices, int n_dev, mcpt_multi** out);
+MCPT_API void mcpt_multi_destroy(mcpt_multi* m);
+MCPT_API int mcpt_multi_size(const mcpt_multi* m);
+MCPT_API mcpt_ctx* mcpt_multi_ctx(mcpt_multi* m, int i);   /* borrowed: GPU i's context (parity hooks) */
+MCPT_API int mcpt_multi_set_seed(mcpt_multi* m, uint64_t seed);
+MCPT_API int mcpt_multi_upload_scene(mcpt_multi* m, const mcpt_scene_desc* scene);
+MCPT_API int mcpt_multi_load_scene_gpu(mcpt_multi* m, const char* path, const char* name, mcpt_camera* camera_out);
+MCPT_API int mcpt_multi_build_bvh(mcpt_multi* m, float* ms_out);
+MCPT_API int mcpt_multi_render(mcpt_multi* m, const mcpt_camera* cam, int width, int height, int spp, int mode, int flags,
+                               float* rgb_out, mcpt_stats* stats);
+MCPT_API int mcpt_multi_render_png(mcpt_multi* m, const mcpt_camera* cam, int width, int height, int spp, int mode, int flags,
+                                   const char* file, mcpt_stats* stats);
+/* render_scene over n_gpus GPUs (0 = every visible GPU, rounded down to a power of two <= 8). */
+MCPT_API int mcpt_render_scene_multi(const char* path, const char* name, int spp, const char* out_dir, int n_gpus);
 
 #ifdef __cplusplus
 }

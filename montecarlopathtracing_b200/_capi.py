@@ -42,7 +42,7 @@ class Hit(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("samples", C.c_double), ("rays", C.c_double), ("node_visits", C.c_double), ("tri_tests", C.c_double),
                 ("render_ms", C.c_float), ("build_ms", C.c_float), ("kernel_launches", C.c_int32), ("integrate_ms", C.c_float),
-                ("trace_ms", C.c_float), ("trace_launches", C.c_int32), ("build_launches", C.c_int32), ("reserved", C.c_int32)]
+                ("trace_ms", C.c_float), ("trace_launches", C.c_int32), ("build_launches", C.c_int32), ("exchange_ms", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if not k.startswith("_")}
@@ -85,7 +85,28 @@ SIGNATURES = {
     "mcpt_render_chunks": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                      C.c_int, C.c_void_p, C.POINTER(Stats)]),
     "mcpt_sum_partials": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_void_p]),
+    "mcpt_measure_read_bandwidth": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.POINTER(C.c_float)]),
+    "mcpt_comm_unique_id": (C.c_int, [C.c_char_p]),
+    "mcpt_comm_init": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p]),
+    "mcpt_comm_destroy": (C.c_int, [C.c_void_p]),
+    "mcpt_render_dist": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                   C.POINTER(Stats)]),
+    "mcpt_device_image": (C.c_void_p, [C.c_void_p]),
+    "mcpt_multi_create": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]),
+    "mcpt_multi_destroy": (None, [C.c_void_p]),
+    "mcpt_multi_size": (C.c_int, [C.c_void_p]),
+    "mcpt_multi_ctx": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "mcpt_multi_set_seed": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "mcpt_multi_upload_scene": (C.c_int, [C.c_void_p, C.POINTER(SceneDesc)]),
+    "mcpt_multi_load_scene_gpu": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.POINTER(Camera)]),
+    "mcpt_multi_build_bvh": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
+    "mcpt_multi_render": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                    C.POINTER(Stats)]),
+    "mcpt_multi_render_png": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p,
+                                        C.POINTER(Stats)]),
+    "mcpt_render_scene_multi": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int]),
 }
+COMM_ID_BYTES = 128
 
 _lib = None
 

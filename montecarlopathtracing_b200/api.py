@@ -234,10 +234,110 @@ class Context:
     def sum_partials(self, d_partials_ptr, n, count, scale, d_out_ptr):
         check(lib().mcpt_sum_partials(self._c, C.c_void_p(d_partials_ptr), n, count, scale, C.c_void_p(d_out_ptr)))
 
+    def measure_read_bandwidth(self, working_set_bytes, repeats=8):
+        """GB/s of a 16-B-vector, L1-bypassing read sweep over a working set of that size (L2 below 126 MB, HBM far above)."""
+        g = C.c_float()
+        check(lib().mcpt_measure_read_bandwidth(self._c, int(working_set_bytes), int(repeats), C.byref(g)))
+        return g.value
 
-def render_scene(path, filename, spp, out_dir=None, device=0):
-    """render_scene(path, filename, spp) of MTPC/MTPC.cpp:35: writes <out_dir><filename>-SPP<spp>.png."""
-    check(lib().mcpt_render_scene(path.encode(), filename.encode(), int(spp), out_dir.encode() if out_dir else None, device))
+    # ---- multi-GPU, one process per GPU (SURVEY.md 8(e)): the exchange and the fixed-order sum live in libmcpt.so ----
+    def comm_init(self, world, rank, comm_id):
+        """Join this context to the render's NCCL communicator; comm_id = the 128 bytes rank 0 got from comm_unique_id()."""
+        check(lib().mcpt_comm_init(self._c, int(world), int(rank), bytes(comm_id)))
+
+    def comm_destroy(self):
+        check(lib().mcpt_comm_destroy(self._c))
+
+    def render_dist(self, camera, spp, width=0, height=0, mode=capi.MODE_WAVEFRONT, flags=0, out=None, to_host=True):
+        """Collective render over the communicator's ranks.  Rank 0 returns the mean image (H,W,3) float32 (host buffer `out`, or
+        None with to_host=False: the image stays on the device, see device_image_ptr); other ranks return None."""
+        w = width if width > 0 else camera.width
+        h = height if height > 0 else camera.height
+        st = capi.Stats()
+        ptr = None
+        if to_host:
+            if out is None:
+                out = np.empty((h, w, 3), np.float32)
+            ptr = out.ctypes.data
+        check(lib().mcpt_render_dist(self._c, C.byref(camera), width, height, spp, mode, flags, ptr, C.byref(st)))
+        self.last_stats = st
+        return out if to_host else None
+
+    def device_image_ptr(self):
+        return lib().mcpt_device_image(self._c)
+
+
+def comm_unique_id():
+    """128-byte NCCL id made by rank 0; broadcast it to every rank (torch.distributed, MPI, a file) and pass it to comm_init."""
+    buf = C.create_string_buffer(capi.COMM_ID_BYTES)
+    check(lib().mcpt_comm_unique_id(buf))
+    return buf.raw
+
+
+class MultiContext:
+    """One process driving n GPUs (mcpt_multi_*): ncclCommInitAll, SPP split, one exchange, fixed-order sum."""
+
+    def __init__(self, n_gpus, devices=None):
+        self._m = C.c_void_p()
+        devs = (C.c_int * n_gpus)(*devices) if devices is not None else None
+        check(lib().mcpt_multi_create(devs, int(n_gpus), C.byref(self._m)))
+        self.n_gpus = n_gpus
+        self.last_stats = capi.Stats()
+
+    def close(self):
+        if self._m:
+            lib().mcpt_multi_destroy(self._m)
+            self._m = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_seed(self, seed):
+        check(lib().mcpt_multi_set_seed(self._m, C.c_uint64(seed)))
+
+    def upload_scene(self, desc):
+        if isinstance(desc, HostScene):
+            desc = desc.desc
+        check(lib().mcpt_multi_upload_scene(self._m, C.byref(desc)))
+
+    def load_scene_gpu(self, path, name):
+        cam = capi.Camera()
+        check(lib().mcpt_multi_load_scene_gpu(self._m, path.encode(), name.encode(), C.byref(cam)))
+        return cam
+
+    def build_bvh(self):
+        ms = C.c_float()
+        check(lib().mcpt_multi_build_bvh(self._m, C.byref(ms)))
+        return ms.value
+
+    def render(self, camera, spp, width=0, height=0, mode=capi.MODE_WAVEFRONT, flags=0, out=None):
+        w = width if width > 0 else camera.width
+        h = height if height > 0 else camera.height
+        if out is None:
+            out = np.empty((h, w, 3), np.float32)
+        st = capi.Stats()
+        check(lib().mcpt_multi_render(self._m, C.byref(camera), width, height, spp, mode, flags, out.ctypes.data, C.byref(st)))
+        self.last_stats = st
+        return out
+
+    def render_png(self, camera, spp, file, width=0, height=0, mode=capi.MODE_WAVEFRONT, flags=0):
+        st = capi.Stats()
+        check(lib().mcpt_multi_render_png(self._m, C.byref(camera), width, height, spp, mode, flags, file.encode(), C.byref(st)))
+        self.last_stats = st
+        return st
+
+
+def render_scene(path, filename, spp, out_dir=None, device=0, gpus=1):
+    """render_scene(path, filename, spp) of MTPC/MTPC.cpp:35: writes <out_dir><filename>-SPP<spp>.png (gpus > 1: SPP split over
+    that many GPUs of this process, gpus = 0: every visible GPU; the same PNG bytes)."""
+    od = out_dir.encode() if out_dir else None
+    if gpus == 1:
+        check(lib().mcpt_render_scene(path.encode(), filename.encode(), int(spp), od, device))
+    else:
+        check(lib().mcpt_render_scene_multi(path.encode(), filename.encode(), int(spp), od, int(gpus)))
     return True
 
 

@@ -23,7 +23,7 @@ NVCC_FLAGS = ARCH + ["-lineinfo", "-O3", "-std=c++17", "-ccbin", CXX, "-Xcompile
 NVCC_FLAGS += os.environ.get("MCPT_NVCC_EXTRA", "").split()   # developer knob for A/B builds (e.g. -DMCPT_SHADE_MIN_CTAS=5)
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall"]
 
-CU_SOURCES = {"lbvh.cu": ["--fmad=false"], "ploc.cu": [], "wide.cu": [], "render.cu": [], "wavefront.cu": [], "png_device.cu": [], "obj_ingest.cu": [], "api.cu": []}
+CU_SOURCES = {"lbvh.cu": ["--fmad=false"], "ploc.cu": [], "wide.cu": [], "render.cu": [], "wavefront.cu": [], "png_device.cu": [], "obj_ingest.cu": [], "api.cu": [], "multigpu.cu": [], "microbench.cu": []}
 CPP_SOURCES = ["scene_loader.cpp", "png_writer.cpp", "render_scene.cpp", "mcpt_error.cpp"]
 
 
@@ -68,7 +68,7 @@ def build(force=False, verbose=False):
             if verbose and out.strip():
                 print(out)
     if force or jobs or not os.path.exists(LIB):
-        _run([NVCC] + ARCH + ["-shared", "-ccbin", CXX, "-o", LIB] + objs + ["-cudart", "static"])
+        _run([NVCC] + ARCH + ["-shared", "-ccbin", CXX, "-o", LIB] + objs + ["-cudart", "static", "-ldl", "-lpthread"])
     cli_src = os.path.join(HOST, "mcpt_cli.cpp")
     if not TAG and os.path.exists(cli_src) and (force or _newer(CLI, [cli_src, LIB])):
         _run([CXX] + CXX_FLAGS + [cli_src, "-o", CLI, "-L" + HERE, "-lmcpt", "-Wl,-rpath,$ORIGIN"])

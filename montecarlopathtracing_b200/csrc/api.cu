@@ -15,44 +15,11 @@
 #include <type_traits>
 #include <unordered_map>
 #include <vector>
-#include "lbvh.h"
-#include "render.h"
-#include "obj_ingest.h"
+#include "context.h"
 
 void mcpt_set_error(const char* msg);  // host/mcpt_error.cpp
 
 using namespace mcpt;
-
-#define PIN_RING 4
-
-struct mcpt_ctx {
-    int device = 0;
-    cudaStream_t own_stream = nullptr, stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;  // ev3..ev2 bracket the integrator kernel
-    uint64_t seed = 0;
-    SceneBuffers sb;
-    DMaterial* d_materials = nullptr; DTexture* d_textures = nullptr; unsigned char* d_tex_bytes = nullptr;
-    DLight* d_lights = nullptr; LightTri* d_light_tris = nullptr; float* d_light_cdf = nullptr;
-    int n_materials = 0, n_textures = 0, n_lights = 0;
-    float area0 = 0.f;
-    unsigned long long* d_counters = nullptr;
-    float* d_planes = nullptr; size_t planes_cap = 0;   // scratch: sample-chunk planes
-    float* d_image = nullptr; size_t image_cap = 0;     // scratch: reduced image
-    float* d_dirs = nullptr; size_t dirs_cap = 0;       // scratch: primary ray directions (K7)
-    unsigned char* d_png = nullptr; size_t png_cap = 0; // scratch: device-encoded PNG (+64 B of sums/CRC in front)
-    char* d_wf = nullptr; size_t wf_cap = 0;            // scratch: wavefront slot state + ray queue
-    WfHost wfh;                                         // streams/events of the wavefront loop
-    void* d_io = nullptr; size_t io_cap = 0;            // scratch: rays in / hits out of mcpt_trace
-    char* d_text = nullptr; size_t text_cap = 0;        // scratch: OBJ text of mcpt_ingest_obj
-    DevArena ingest_text, ingest_stmt;                  // scratch: ingest temporaries
-    DevArena scene_arena, tables_arena;                 // grow-only: a re-upload of a scene that fits allocates nothing
-    char* h_pin[PIN_RING] = {}; cudaEvent_t pin_ev[PIN_RING] = {};   // pinned ring of mcpt_ingest_obj_file (one buffer per reader thread)
-    int last_ingest_launches = 0;
-    float last_build_ms = 0.f;
-    int last_build_launches = 0;
-    int coop_blocks[2] = {0, 0};   // co-resident CTAs of wide_collapse_kernel / ploc_rounds_kernel on this device
-    bool scene_loaded = false;
-};
 
 namespace {
 int fail_cuda(cudaError_t e, const char* what) {
@@ -347,6 +314,8 @@ MCPT_API void mcpt_destroy(mcpt_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    mcpt_comm_release(c);
+    cudaFree(c->d_stacked);
     free_scene(c);
     cudaFree(c->d_counters); cudaFree(c->d_planes); cudaFree(c->d_image); cudaFree(c->d_io); cudaFree(c->d_dirs); cudaFree(c->d_wf); cudaFree(c->d_png); cudaFree(c->d_text); c->ingest_text.release(); c->ingest_stmt.release(); c->scene_arena.release(); c->tables_arena.release(); c->wfh.destroy();
     for (int k = 0; k < PIN_RING; k++) { if (c->h_pin[k]) cudaFreeHost(c->h_pin[k]); if (c->pin_ev[k]) cudaEventDestroy(c->pin_ev[k]); }
@@ -590,7 +559,7 @@ namespace {
 void fill_stats(mcpt_ctx* c, mcpt_stats* st, double samples, const unsigned long long cnt[3], float ms, int launches) {
     if (!st) return;
     st->samples = samples; st->rays = (double)cnt[0]; st->node_visits = (double)cnt[1]; st->tri_tests = (double)cnt[2];
-    st->render_ms = ms; st->build_ms = c->last_build_ms; st->build_launches = c->last_build_launches; st->reserved = 0; st->kernel_launches = launches; st->integrate_ms = 0.f;
+    st->render_ms = ms; st->build_ms = c->last_build_ms; st->build_launches = c->last_build_launches; st->exchange_ms = 0.f; st->kernel_launches = launches; st->integrate_ms = 0.f;
     st->trace_ms = 0.f; st->trace_launches = 0;
 }
 // generateImg's camera basis (MTPC/pathTracing.cpp:276-294), in double on the host

@@ -309,12 +309,13 @@ def test_tie_heavy_input_builds_quickly_and_correctly(gpu_ctx):
     ms = gpu_ctx.build_bvh()
     assert ms < 50.0, "tie-heavy build took %.1f ms" % ms
     nodes, origin, cell = gpu_ctx.get_wide_tree()
-    tri_lo, tri_hi = pos.min(axis=1), pos.max(axis=1)
-    check_wide_tree(nodes, origin, cell, n, tri_lo, tri_hi)
+    _, _, face_sorted = gpu_ctx.get_morton()
+    p = pos[face_sorted].astype(np.float32).astype(np.float64)
+    check_wide_tree(nodes, origin.astype(np.float64), cell.astype(np.float64), n, p.min(axis=1), p.max(axis=1))
     # a ray into the stack of n/2 identical triangles: the reference's tie rule picks the lowest sorted leaf
     hits = gpu_ctx.trace(np.array([[0.002, 0.002, 1.0, 1e-4, 1e-4, -1.0]], np.float32))
-    _, _, face_sorted = gpu_ctx.get_morton()
     assert hits["leaf"][0] >= 0 and hits["tri"][0] == face_sorted[hits["leaf"][0]]
+    tri_lo = pos.min(axis=1)
     same_box = np.nonzero((tri_lo == tri_lo[hits["tri"][0]]).all(axis=1))[0]
     leaf_of = np.empty(n, np.int64); leaf_of[face_sorted] = np.arange(n)
     assert hits["leaf"][0] == leaf_of[same_box].min()

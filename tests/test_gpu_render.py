@@ -96,6 +96,7 @@ def test_image_independent_of_gpu_count(gpu_ctx, scenes, w, h, spp):
         torch.cuda.synchronize()
         got = out.cpu().numpy().reshape(h, w, 3)
         assert np.array_equal(got, base), "R=%d differs" % R
+    gpu_ctx.use_own_stream()   # gpu_backend had put the context on torch's stream
 
 
 def test_render_scene_writes_reference_style_png(gpu_ctx, tmp_path):
@@ -190,6 +191,7 @@ def test_wavefront_chunk_ranges_are_gpu_count_independent(gpu_ctx, scenes):
         out = sum_partials(torch.cat(parts), R, 1.0 / spp)
         torch.cuda.synchronize()
         assert np.array_equal(out.cpu().numpy().reshape(h, w, 3), base), "R=%d differs" % R
+    gpu_ctx.use_own_stream()
 
 
 @pytest.mark.parametrize("h,w", [(1, 1), (37, 301), (270, 480), (1080, 1920)])
@@ -255,3 +257,51 @@ def test_image_independent_of_the_number_of_path_slots(gpu_ctx, scenes, name, w,
             monkeypatch.setenv("MCPT_WF_SLOTS", target)
         img = gpu_ctx.render(s.camera, spp, w, h, mode=M.MODE_WAVEFRONT)
         assert np.array_equal(img.view(np.uint32), base.view(np.uint32)), "MCPT_WF_SLOTS=%s differs" % target
+
+
+def test_stream_ordering_with_the_callers_stream(gpu_ctx, scenes):
+    """mcpt_set_stream takes the handle as given — torch's default stream IS handle 0 — so work torch enqueues before a call is
+    seen by the call and work after it sees the call's result, with no synchronize in between (round 1 treated NULL as "own
+    stream" and passed this only by timing)."""
+    import torch
+    s = scenes["cornell-box"]
+    _load(gpu_ctx, s)
+    gpu_ctx.set_seed(5)
+    w, h, spp = 320, 200, 16
+    base = gpu_ctx.render(s.camera, spp, w, h)
+    count = w * h * 3
+    gpu_ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    try:
+        for R in (2, 8):
+            parts = torch.empty((R, count), dtype=torch.float32, device="cuda")
+            for r in range(R):
+                gpu_ctx.render_chunks(s.camera, spp, r * 64 // R, (r + 1) * 64 // R, parts[r].data_ptr(), width=w, height=h)
+            big = torch.randn(64 << 20, device="cuda")          # keeps the stream busy in front of the copy below
+            stacked = torch.empty_like(parts)
+            for _ in range(8):
+                big = big * 1.0001
+            stacked.copy_(parts)                                   # enqueued, not finished, when sum_partials is called
+            out = torch.empty(count, dtype=torch.float32, device="cuda")
+            gpu_ctx.sum_partials(stacked.data_ptr(), R, count, 1.0 / spp, out.data_ptr())
+            host = out.cpu().numpy().reshape(h, w, 3)              # torch's copy is ordered behind the sum kernel
+            assert np.array_equal(host, base), "R=%d differs" % R
+    finally:
+        gpu_ctx.use_own_stream()
+
+
+def test_render_dist_on_one_rank_equals_render(gpu_ctx, scenes):
+    """mcpt_render_dist with a world of one (no NCCL needed): same image and ray count as mcpt_render."""
+    s = scenes["veach-mis"]
+    _load(gpu_ctx, s)
+    gpu_ctx.set_seed(8)
+    base = gpu_ctx.render(s.camera, 12, 200, 150)
+    rays = gpu_ctx.last_stats.rays
+    gpu_ctx.comm_init(1, 0, bytes(128))
+    img = gpu_ctx.render_dist(s.camera, 12, 200, 150)
+    assert np.array_equal(img, base) and gpu_ctx.last_stats.rays == rays and gpu_ctx.last_stats.exchange_ms >= 0
+    assert gpu_ctx.render_dist(s.camera, 12, 200, 150, to_host=False) is None and gpu_ctx.device_image_ptr()
+    gpu_ctx.comm_destroy()
+    with pytest.raises(M.McptError, match="mcpt_comm_init first"):
+        gpu_ctx.render_dist(s.camera, 12, 200, 150)
+    with pytest.raises(M.McptError, match="1, 2, 4 or 8"):
+        gpu_ctx.comm_init(3, 0, bytes(128))
