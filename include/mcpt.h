@@ -106,7 +106,8 @@ typedef struct mcpt_stats {
 
 enum { MCPT_MODE_MEGAKERNEL = 0, MCPT_MODE_WAVEFRONT = 1 };
 enum { MCPT_FLAG_COUNT = 1,            /* count node visits / triangle tests (slower) */
-       MCPT_FLAG_NO_PRIMARY_REUSE = 2  /* re-trace the (identical, Q4) primary ray for every sample */ };
+       MCPT_FLAG_NO_PRIMARY_REUSE = 2, /* re-trace the (identical, Q4) primary ray for every sample */
+       MCPT_FLAG_NO_SHADOW_EARLY_OUT = 4 /* walk every shadow ray to its closest hit even after its answer is settled (same image, bit for bit) */ };
 
 /* Number of sample chunks a render is always cut into (chunk k = samples [k*spp/C, (k+1)*spp/C)); GPU r of R in
  * {1,2,4,8} owns chunks [r*C/R,(r+1)*C/R).  Every chunk is accumulated sequentially into its own plane and the planes are

@@ -147,8 +147,10 @@ int upload_tables(mcpt_ctx* c, const mcpt_scene_desc* d, const std::vector<std::
         L.mat_id = d->lights[l].mat_id; L.first = (int)ltris.size(); L.count = 0;
         for (int k = 0; k < 3; k++) L.radiance[k] = (float)d->lights[l].radiance[k];
         double total = 0;
+        float blo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, bhi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
         for (size_t j = 0; j < lpos[l].size() / 9; j++) {
             const double* p = &lpos[l][9 * j]; const double* q = &lnrm[l][9 * j];
+            for (int k = 0; k < 9; k++) { blo[k % 3] = std::min(blo[k % 3], (float)p[k]); bhi[k % 3] = std::max(bhi[k % 3], (float)p[k]); }
             total += face_area(p);
             cdf.push_back((float)total);
             LightTri t;
@@ -161,6 +163,11 @@ int upload_tables(mcpt_ctx* c, const mcpt_scene_desc* d, const std::vector<std::
             L.count++;
         }
         areas[l] = total; L.area = (float)total;
+        // box of the light material's triangles, pushed out past the rounding of the traversal triangles (v0 + e1 in FP32)
+        for (int k = 0; k < 3; k++) {
+            const float pad = 1.0e-5f * std::max(std::fabs(blo[k]), std::fabs(bhi[k])) + 1.0e-6f;
+            L.box_lo[k] = blo[k] - pad; L.box_hi[k] = bhi[k] + pad;
+        }
     }
     c->area0 = d->n_lights > 0 ? (float)areas[0] : 0.f;
     for (int l = 0; l < d->n_lights; l++) {   // entries reachable by rnd <= area0 (quirk Q6): bounds the binary search
@@ -591,6 +598,7 @@ DCamera make_camera(const mcpt_camera* cam, int width, int height) {
 int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, int spp, int cb, int ce, int mode, int flags,
                    int* launches) {
     if (mode != MCPT_MODE_MEGAKERNEL && mode != MCPT_MODE_WAVEFRONT) return fail_arg("render: unknown mode");
+    if (getenv("MCPT_NO_SHADOW_EARLY_OUT")) flags |= MCPT_FLAG_NO_SHADOW_EARLY_OUT;   // developer A/B switch (same image either way)
     const int nch = ce - cb;
     const size_t plane = (size_t)width * height * 3;
     CU(grow(c->d_planes, c->planes_cap, sizeof(float) * plane * nch));

@@ -58,6 +58,8 @@ struct DLight {
     int first;        // first entry in light_tris / light_cdf
     int count;        // triangles of that material
     int n_search;     // entries whose CDF can be selected by rnd in [0, area of light 0) (quirk Q6)
+    float box_lo[3], box_hi[3];   // AABB of every triangle carrying this light's material, padded outward (shadow-ray early-out)
+    int _pad[2];
 };
 
 struct DeviceScene {

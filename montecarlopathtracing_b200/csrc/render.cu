@@ -48,7 +48,7 @@ int launch_raygen(const DCamera& cam, float* d_dirs, cudaStream_t stream) {
 enum { PH_PRIMARY = -2, PH_NEWSAMPLE = -1 };
 
 template <bool COUNT, bool REUSE_PRIMARY>
-__global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
+__global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P, const bool early_out) {
     const DeviceScene& sc = P.scene;
     const int W = P.cam.width, H = P.cam.height;
     const int tiles_x = (W + 7) >> 3, tiles_y = (H + 3) >> 2, n_tiles = tiles_x * tiles_y;
@@ -125,7 +125,8 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
             if (done) break;
             // ---- the single traversal site ----
             n_rays++;
-            const Hit h = trace_closest<COUNT>(sc, ro, rd, rtmax, n_nodes, n_tris);
+            const Occluder oc = (early_out && phase >= 0 && phase < nl) ? shadow_occluder(sc.lights[phase], ro, rd, rtmax) : no_occluder();
+            const Hit h = trace_closest<COUNT>(sc, ro, rd, rtmax, n_nodes, n_tris, oc);
             // ---- consume the result ----
             if (phase == PH_PRIMARY) {
                 if (REUSE_PRIMARY) { hit0 = h; have_hit0 = true; }
@@ -339,10 +340,11 @@ int launch_megakernel(const RenderParams& P, int flags, cudaStream_t stream) {
     const long long blocks = (warps * 32 + tpb - 1) / tpb;
     if (blocks <= 0 || blocks > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
     const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
-    if (count && reuse) pt_megakernel<true, true><<<(unsigned)blocks, tpb, 0, stream>>>(P);
-    else if (count) pt_megakernel<true, false><<<(unsigned)blocks, tpb, 0, stream>>>(P);
-    else if (reuse) pt_megakernel<false, true><<<(unsigned)blocks, tpb, 0, stream>>>(P);
-    else pt_megakernel<false, false><<<(unsigned)blocks, tpb, 0, stream>>>(P);
+    const bool eo = !(flags & MCPT_FLAG_NO_SHADOW_EARLY_OUT);
+    if (count && reuse) pt_megakernel<true, true><<<(unsigned)blocks, tpb, 0, stream>>>(P, eo);
+    else if (count) pt_megakernel<true, false><<<(unsigned)blocks, tpb, 0, stream>>>(P, eo);
+    else if (reuse) pt_megakernel<false, true><<<(unsigned)blocks, tpb, 0, stream>>>(P, eo);
+    else pt_megakernel<false, false><<<(unsigned)blocks, tpb, 0, stream>>>(P, eo);
     return (int)cudaGetLastError();
 }
 

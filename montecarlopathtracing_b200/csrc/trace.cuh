@@ -135,9 +135,35 @@ __device__ __forceinline__ void node4_step(const QNode4* __restrict__ nodes, int
     if (s0 == 0xFFFFFFFFu) node = stack[--sp];
 }
 
+// Shadow rays (MTPC/pathTracing.cpp:202-215) ask one question: does the CLOSEST hit carry the light's material?  The answer is
+// known to be "no" as soon as a triangle of ANOTHER material is hit in front of the box that holds every triangle of the light's
+// material (DLight::box_*): nothing of that material can be closer.  occl_t = the ray's entry distance into that box, shrunk a
+// little (so rounding cannot make it late); a non-shadow ray has occl_t < 0 and the test never fires.  Exact, not an any-hit
+// approximation: the visibility bit — hence the image — is the same with and without it (tests: bit-identity of the integrators
+// with MCPT_FLAG_NO_SHADOW_EARLY_OUT).
+struct Occluder { float t; int light_mat; };
+__device__ __forceinline__ Occluder no_occluder() { Occluder o; o.t = -1.0f; o.light_mat = -1; return o; }
+__device__ __forceinline__ Occluder shadow_occluder(const DLight& L, const float3 o, const float3 d, const float tmax) {
+    const float ooeps = 1.0e-24f;
+    const float ix = __frcp_approx(fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x));
+    const float iy = __frcp_approx(fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y));
+    const float iz = __frcp_approx(fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z));
+    const float x0 = (L.box_lo[0] - o.x) * ix, x1 = (L.box_hi[0] - o.x) * ix;
+    const float y0 = (L.box_lo[1] - o.y) * iy, y1 = (L.box_hi[1] - o.y) * iy;
+    const float z0 = (L.box_lo[2] - o.z) * iz, z1 = (L.box_hi[2] - o.z) * iz;
+    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+    Occluder oc; oc.light_mat = L.mat_id;
+    // a ray that misses the box cannot hit the light's material at all: every hit occludes
+    oc.t = (tn <= tf * 1.00001f + 1.0e-6f) ? tn * 0.99999f - 1.0e-6f : tmax;
+    return oc;
+}
+
 // Möller–Trumbore on sorted triangle k; keeps it in `best` if it is the closer hit (ties: lower leaf index).
+// Returns true when a shadow ray's question is settled by this hit (see Occluder).
 template <bool COUNT>
-__device__ __forceinline__ void tri_test(const TriGeom* __restrict__ tris, const int k, const RayCtx& r, Hit& best, unsigned& n_tris) {
+__device__ __forceinline__ bool tri_test(const TriGeom* __restrict__ tris, const int k, const RayCtx& r, Hit& best, unsigned& n_tris,
+                                         const Occluder oc = Occluder{-1.0f, -1}) {
     const float4 v0 = __ldg(&tris[k].v0m);
     const float4 e1 = __ldg(&tris[k].e1f);
     const float4 e2 = __ldg(&tris[k].e2);
@@ -158,8 +184,10 @@ __device__ __forceinline__ void tri_test(const TriGeom* __restrict__ tris, const
         // only for the few candidates at grazing d.x.
         if (fabsf(r.d.x * t) > 1.0e-12f * fabsf(r.o.x) || __dadd_rn((double)r.o.x, __dmul_rn((double)r.d.x, (double)t)) != (double)r.o.x) {
             best.t = t; best.u = u; best.v = v; best.k = k;
+            return t < oc.t && __float_as_int(v0.w) != oc.light_mat;
         }
     }
+    return false;
 }
 
 // Leaf references of the traversal nodes (device_types.cuh QNode): ~(k | delta << 26) = triangle k and, when delta != 0,
@@ -167,24 +195,26 @@ __device__ __forceinline__ void tri_test(const TriGeom* __restrict__ tris, const
 __device__ __forceinline__ int leaf_first(const int ref) { return ~ref & ((1 << MCPT_LEAF_BITS) - 1); }
 __device__ __forceinline__ int leaf_delta(const int ref) { return (~ref >> MCPT_LEAF_BITS) & 15; }
 template <bool COUNT>
-__device__ __forceinline__ void leaf_test(const TriGeom* __restrict__ tris, const int ref, const RayCtx& r, Hit& best, unsigned& n_tris) {
+__device__ __forceinline__ bool leaf_test(const TriGeom* __restrict__ tris, const int ref, const RayCtx& r, Hit& best, unsigned& n_tris,
+                                          const Occluder oc = Occluder{-1.0f, -1}) {
     const int k = leaf_first(ref), dk = leaf_delta(ref);
-    tri_test<COUNT>(tris, k, r, best, n_tris);
-    if (dk) tri_test<COUNT>(tris, k + dk, r, best, n_tris);
+    bool settled = tri_test<COUNT>(tris, k, r, best, n_tris, oc);
+    if (dk) settled = tri_test<COUNT>(tris, k + dk, r, best, n_tris, oc) || settled;
+    return settled;
 }
 
-// One leaf step: test the triangle(s) of leaf reference `node`, then pop.
+// One leaf step: test the triangle(s) of leaf reference `node`, then pop (or stop: a settled shadow ray).
 template <bool COUNT>
 __device__ __forceinline__ void leaf_step(const TriGeom* __restrict__ tris, int& node, const RayCtx& r, Hit& best, int* stack,
-                                          int& sp, unsigned& n_tris) {
-    leaf_test<COUNT>(tris, node, r, best, n_tris);
-    node = stack[--sp];
+                                          int& sp, unsigned& n_tris, const Occluder oc) {
+    const bool settled = leaf_test<COUNT>(tris, node, r, best, n_tris, oc);
+    node = settled ? MCPT_SENT : stack[--sp];
 }
 
 // Closest hit of one ray, one ray per thread from start to finish (megakernel and the batch kernel of seam 2).
 template <bool COUNT>
 __device__ __forceinline__ Hit trace_closest(const DeviceScene& sc, const float3 o, const float3 d, const float tmax,
-                                             unsigned& n_nodes, unsigned& n_tris) {
+                                             unsigned& n_nodes, unsigned& n_tris, const Occluder oc = Occluder{-1.0f, -1}) {
     Hit best; best.t = tmax; best.u = 0.f; best.v = 0.f; best.k = -1;
     if (d.x == 0.0f) return best;
     const RayCtx r = ray_setup(o, d, sc.qgrid);
@@ -198,7 +228,7 @@ __device__ __forceinline__ Hit trace_closest(const DeviceScene& sc, const float3
 #else
         if (node >= 0) node_step<COUNT>(sc.qnodes, node, r, best.t, stack, sp, n_nodes);
 #endif
-        else leaf_step<COUNT>(sc.tri, node, r, best, stack, sp, n_tris);
+        else leaf_step<COUNT>(sc.tri, node, r, best, stack, sp, n_tris, oc);
     }
     return best;
 }

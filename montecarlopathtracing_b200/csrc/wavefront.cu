@@ -38,6 +38,7 @@ struct WfBuffers {
     float4* rd;      // direction of the extend ray in flight (the next vertex's -wo)
     float4* pend;    // [light][slot]: throughput * unshadowed NEE contribution of the vertex in flight
     unsigned* vis;   // shadow-ray results, bit l = light l visible
+    unsigned char* warp_done;  // [slot / 32]: every slot of that warp is DONE (or outside the image): wf_shade reads nothing else
     float4* ray_o;   // queue: origin, tmax
     float4* ray_d;   // queue: direction, id = slot | (kind << 26), kind 0 = primary/extend, l+1 = shadow ray of light l
     unsigned* counters;
@@ -110,8 +111,19 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
     const int chunk_first = P.chunk_begin + group * P.chunks_per_thread, chunk_end = chunk_first + P.chunks_per_thread;
     float4 ss_in = make_float4(0.f, 0.f, 0.f, 0.f), h0_in = ss_in, hit_in = ss_in, L_in = ss_in, rd_in = ss_in;
     unsigned vis_in = 0u;
+    // Finished warps cost one byte: at 3840 x 2160 the 16:9 frame looks past the box on both sides, ~45 % of the slots are DONE
+    // after the first two iterations, and re-reading + re-writing their 16-B meta word every iteration was a quarter of the
+    // kernel's DRAM traffic.  A CTA whose eight warps are all finished leaves before the queue barriers.
+    bool warp_was_done = false;
+    if (iter != 0) {
+        unsigned char f = 0;
+        if (lane == 0 && slot < B.slot_end) f = __ldcg(&B.warp_done[slot >> 5]);
+        warp_was_done = __shfl_sync(0xffffffffu, (int)f, 0) != 0 || (slot - lane) >= B.slot_end;
+        if (__syncthreads_and(warp_was_done)) return;
+    }
+    bool was_done = warp_was_done;
 
-    if (valid) {
+    if (valid && !warp_was_done) {
         cam_d = f3(__ldg(P.cam_dirs + 3 * (size_t)pixel), __ldg(P.cam_dirs + 3 * (size_t)pixel + 1), __ldg(P.cam_dirs + 3 * (size_t)pixel + 2));
         if (iter == 0) {
             state = WF_NEW; chunk = chunk_first; s = (int)((long long)chunk * P.spp / MCPT_NUM_CHUNKS);
@@ -125,6 +137,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
             state = meta & 3u; lobe = (meta >> 2) & 3u; has_extend = (meta >> 4) & 1u; have_hit0 = (meta >> 5) & 1u;
             bounce = (meta >> 8) & 0xffu; chunk = (int)(meta >> 16);
             beta = f3(bm.x, bm.y, bm.z);
+            was_done = state == WF_DONE;
             if (state != WF_DONE) {
                 sum = f3(ss_in.x, ss_in.y, ss_in.z); s = __float_as_int(ss_in.w);
                 if (have_hit0) { hit0.t = h0_in.x; hit0.u = h0_in.y; hit0.v = h0_in.z; hit0.k = __float_as_int(h0_in.w); }
@@ -224,8 +237,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
         push_ray(ext || emit_primary, B, tail, o, d, 3.0e38f, (unsigned)slot, push_sh, nl);
     }
     // ---- store the slot ----
-    if (valid) {
-        const bool was_done_before = (iter != 0) && !have_vertex && !emit_primary && state == WF_DONE;
+    if (valid && !was_done) {
         __stcg(&B.beta_m[slot], make_float4(beta.x, beta.y, beta.z, __uint_as_float(pack_meta(state, lobe, has_extend, have_hit0, bounce, chunk))));
         if (state != WF_DONE) {
             __stcg(&B.sum_s[slot], make_float4(sum.x, sum.y, sum.z, __int_as_float(s)));
@@ -235,11 +247,15 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
             }
             if (store_hit0) __stcg(&B.hit0[slot], make_float4(hit0.t, hit0.u, hit0.v, __int_as_float(hit0.k)));
         }
-        (void)was_done_before;
     } else if (slot < B.slot_end && iter == 0) {
         __stcg(&B.beta_m[slot], make_float4(0.f, 0.f, 0.f, __uint_as_float(pack_meta(WF_DONE, 0, false, false, 0, 0))));
     }
-    const int alive = __syncthreads_count(valid && state != WF_DONE);
+    const bool live = valid && state != WF_DONE;
+    if (!warp_was_done) {
+        const bool all_done = __all_sync(0xffffffffu, !live);
+        if (lane == 0 && slot < B.slot_end && (all_done || iter == 0)) __stcg(&B.warp_done[slot >> 5], (unsigned char)all_done);
+    }
+    const int alive = __syncthreads_count(live);
     if (threadIdx.x == 0 && alive) atomicAdd(B.counters + WFC_ALIVE + par, (unsigned)alive);
 }
 
@@ -262,7 +278,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
 template <bool COUNT>
 __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const DeviceScene sc, const WfBuffers B, const int iter, unsigned long long* stats,
                                                 const int refill_min, const int leaf_min, const int block_min,
-                                                const int node_steps) {
+                                                const int node_steps, const bool early_out) {
     const int par = iter & 1;
     const unsigned n = __ldcg(B.counters + WFC_TAIL + par);
     unsigned* head = B.counters + WFC_HEAD + par;
@@ -278,6 +294,7 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
     stack[0] = MCPT_SENT;
     int sp = 1, node = MCPT_SENT;
     unsigned id = 0;
+    Occluder oc = no_occluder();
     bool has_ray = false, exhausted = false;
     auto write_back = [&]() {
         const unsigned slot = id & ((1u << WF_ID_BITS) - 1u), kind = id >> WF_ID_BITS;
@@ -311,6 +328,8 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
                         r = ray_setup(f3(o4), f3(d4), sc.qgrid);
                         best.t = o4.w; best.u = 0.f; best.v = 0.f; best.k = -1;
                         sp = 1; has_ray = true;
+                        const unsigned kind = id >> WF_ID_BITS;
+                        oc = (early_out && kind != 0u) ? shadow_occluder(sc.lights[kind - 1], f3(o4), f3(d4), o4.w) : no_occluder();
                         node = (d4.x == 0.0f) ? MCPT_SENT : sc.root;   // quirk Q2: d.x == 0 hits nothing
                     }
                 }
@@ -349,7 +368,7 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
         }
         if (COUNT && lane == 0) { w_iter++; if (pm != 0u && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) w_tri++; }
         if (has_p && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) {
-            leaf_test<COUNT>(sc.tri, pend, r, best, n_tris);
+            if (leaf_test<COUNT>(sc.tri, pend, r, best, n_tris, oc)) { node = MCPT_SENT; sp = 1; }   // shadow ray settled: occluded
 #if MCPT_PEND2
             pend = pend2; pend2 = 0;
 #else
@@ -381,7 +400,7 @@ int wavefront_slots(const RenderParams& P) {
 
 size_t wavefront_scratch_bytes(int n_slots, int n_lights) {
     const size_t n = (size_t)n_slots;
-    return 6 * align256(16 * n) + align256(16 * n * (size_t)(n_lights > 0 ? n_lights : 1)) + align256(4 * n) +
+    return 6 * align256(16 * n) + align256(16 * n * (size_t)(n_lights > 0 ? n_lights : 1)) + align256(4 * n) + align256(n / 32 + 1) +
            2 * align256(16 * n * (size_t)(n_lights + 1)) + align256(4 * WFC_COUNT * WF_MAX_PIPES);
 }
 
@@ -420,6 +439,7 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
     B0.beta_m = (float4*)take(16 * n); B0.L = (float4*)take(16 * n); B0.rd = (float4*)take(16 * n);
     B0.pend = (float4*)take(16 * n * (size_t)(nl > 0 ? nl : 1));
     B0.vis = (unsigned*)take(4 * n);
+    B0.warp_done = (unsigned char*)take(n / 32 + 1);
     B0.ray_o = (float4*)take(16 * n * (size_t)(nl + 1)); B0.ray_d = (float4*)take(16 * n * (size_t)(nl + 1));
     B0.counters = (unsigned*)take(4 * WFC_COUNT * WF_MAX_PIPES);
     B0.n_slots = n_slots;
@@ -446,6 +466,7 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
     for (int k = 1; k < pipes; k++) WF_CU(cudaStreamWaitEvent(pp[k].st, ev_fork, 0));
 
     const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
+    const bool early_out = !(flags & MCPT_FLAG_NO_SHADOW_EARLY_OUT);
     const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 12) / pipes;   // CTAs of 4 warps, shared by the pipes
     const int refill_min = env_int("MCPT_REFILL_MIN", 12), leaf_min = env_int("MCPT_LEAF_MIN", 1),
               block_min = env_int("MCPT_BLOCK_MIN", 1), node_steps = env_int("MCPT_NODE_STEPS", MCPT_WIDE ? 2 : 4);
@@ -466,8 +487,8 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
                     H.trace_events.push_back(ev);
                 }
                 cudaEventRecord(H.trace_events[2 * n_timed], q.st);
-                if (count) wf_trace<true><<<trace_blocks, 128, 0, q.st>>>(P.scene, q.B, iter, P.counters, refill_min, leaf_min, block_min, node_steps);
-                else wf_trace<false><<<trace_blocks, 128, 0, q.st>>>(P.scene, q.B, iter, P.counters, refill_min, leaf_min, block_min, node_steps);
+                if (count) wf_trace<true><<<trace_blocks, 128, 0, q.st>>>(P.scene, q.B, iter, P.counters, refill_min, leaf_min, block_min, node_steps, early_out);
+                else wf_trace<false><<<trace_blocks, 128, 0, q.st>>>(P.scene, q.B, iter, P.counters, refill_min, leaf_min, block_min, node_steps, early_out);
                 cudaEventRecord(H.trace_events[2 * n_timed + 1], q.st);
                 n_timed++; nlaunch += 2;
             }

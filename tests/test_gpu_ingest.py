@@ -180,3 +180,16 @@ def test_render_scene_entry_point_uses_the_gpu_ingest(gpu_ctx, tmp_path, scenes)
     f = str(tmp_path / "host.png")
     M.write_png(f, gpu_ctx.render(s.camera, 1))
     assert open(f, "rb").read() == open(str(tmp_path / "cornell-box-SPP1.png"), "rb").read()
+
+
+@pytest.mark.parametrize("name", ["cornell-box", "veach-mis", "glass-box"])
+def test_gpu_ingest_equals_what_the_reference_parsed(gpu_ctx, name):
+    """K16-K18 against the arrays the UNMODIFIED reference's read_scene produced (tests/golden/*_scene.npz), bit for bit."""
+    from conftest import GOLDEN, SCENES
+    g = np.load(os.path.join(GOLDEN, name + "_scene.npz"))
+    gpu_ctx.load_scene_gpu(SCENES, name)
+    pos, nrm, uv, mat = gpu_ctx.get_scene_arrays()
+    assert np.array_equal(pos, g["pos"]) and np.array_equal(nrm, g["nrm"]) and np.array_equal(uv, g["uv"])
+    import montecarlopathtracing_b200 as M
+    names = M.HostScene(SCENES, name).material_names
+    assert [names[i] for i in mat] == [str(g["mat_names"][i]) for i in g["mat_index"]]
