@@ -313,6 +313,9 @@ MCPT_API int mcpt_create(int device, mcpt_ctx** out) {
     c->stream = c->own_stream;
     CU(cudaEventCreate(&c->ev0)); CU(cudaEventCreate(&c->ev1)); CU(cudaEventCreate(&c->ev2)); CU(cudaEventCreate(&c->ev3));
     CU(dev_alloc(c->d_counters, 8));
+    CU(cudaStreamCreateWithFlags(&c->build_streams.side, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&c->build_streams.ev_fork, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->build_streams.ev_join, cudaEventDisableTiming));
     *out = c;
     return MCPT_OK;
 }
@@ -328,6 +331,9 @@ MCPT_API void mcpt_destroy(mcpt_ctx* c) {
     for (int k = 0; k < PIN_RING; k++) { if (c->h_pin[k]) cudaFreeHost(c->h_pin[k]); if (c->pin_ev[k]) cudaEventDestroy(c->pin_ev[k]); }
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev2); cudaEventDestroy(c->ev3);
     cudaStreamDestroy(c->own_stream);
+    if (c->build_streams.side) cudaStreamDestroy(c->build_streams.side);
+    if (c->build_streams.ev_fork) cudaEventDestroy(c->build_streams.ev_fork);
+    if (c->build_streams.ev_join) cudaEventDestroy(c->build_streams.ev_join);
     delete c;
 }
 
@@ -478,7 +484,7 @@ MCPT_API int mcpt_build_bvh(mcpt_ctx* c, float* ms_out) {
     c->sb.w4_resident_blocks = c->coop_blocks[0]; c->sb.ploc_resident_blocks = c->coop_blocks[1];   // occupancy queries, once per context
     CU(cudaEventRecord(c->ev0, c->stream));
     int launches = 0;
-    const int e = lbvh_build(c->sb, c->stream, &launches);
+    const int e = lbvh_build(c->sb, c->stream, c->build_streams, &launches);
     if (e) return fail_cuda((cudaError_t)e, "lbvh_build");
     c->coop_blocks[0] = c->sb.w4_resident_blocks; c->coop_blocks[1] = c->sb.ploc_resident_blocks;
     CU(cudaEventRecord(c->ev1, c->stream));

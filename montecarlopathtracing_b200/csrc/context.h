@@ -14,6 +14,7 @@ struct mcpt_ctx {
     int device = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;  // ev3..ev2 bracket the integrator kernel
+    mcpt::BuildStreams build_streams{};                  // side stream + fork/join events of mcpt_build_bvh
     uint64_t seed = 0;
     mcpt::SceneBuffers sb;
     mcpt::DMaterial* d_materials = nullptr; mcpt::DTexture* d_textures = nullptr; unsigned char* d_tex_bytes = nullptr;

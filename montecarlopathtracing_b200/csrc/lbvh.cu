@@ -3,6 +3,7 @@
 // MTPC/sceneManagement.cpp:311-314) and the balanced-tree BVH (MTPC/BVH.cpp:44-132).
 // This file is compiled WITHOUT fused multiply-add (--fmad=false, see build.py): K1's float pipeline
 // must be IEEE-identical to the host's.
+#include <cub/block/block_radix_sort.cuh>
 #include <cub/device/device_radix_sort.cuh>
 #include "lbvh.h"
 #include "quant.cuh"
@@ -85,11 +86,7 @@ __global__ void __launch_bounds__(256) radix_tree_kernel(const uint32_t* __restr
     if (c1 < 0) leaf_parent[gamma + 1] = i; else reinterpret_cast<int*>(&nodes[c1].q[3])[2] = i;
 }
 
-// ---- K3: leaf emit (traversal layout) + bottom-up AABB refit with atomic arrival counters ----------
-// One thread per sorted leaf: gathers the face's FP64 inputs once, writes the 48-B triangle and the
-// 64-B shading record, forms a conservatively padded FP32 box and carries it up the tree.  At each
-// parent the first child to arrive stores its box in the parent's slot and stops; the second one
-// reads the sibling's box back (L2, volatile) and continues with the union.
+// ---- K3: leaf emit (traversal layout, K3a) and bottom-up AABB refit with atomic arrival counters (K3b) ----------
 struct Box3 { float lo[3], hi[3]; };
 
 __device__ __forceinline__ void store_child_box(BvhNode* node, int slot, const Box3& b) {
@@ -106,15 +103,29 @@ __device__ __forceinline__ Box3 load_child_box(const BvhNode* node, int slot) {
     return b;
 }
 
-__global__ void __launch_bounds__(256) emit_refit_kernel(int n, const double* __restrict__ pos, const double* __restrict__ nrm,
-                                                         const double* __restrict__ uv, const int* __restrict__ mat_id,
-                                                         const int* __restrict__ leaf_face, const int* __restrict__ leaf_parent,
-                                                         BvhNode* nodes, unsigned* flags, TriGeom* __restrict__ tri,
-                                                         TriShade* __restrict__ shade, float* __restrict__ root_box,
-                                                         float4* __restrict__ cl_lo, float4* __restrict__ cl_hi, int* __restrict__ w4_queue) {
+// FP32 box of face f's three vertices, pushed outward (> 3 ulp: covers the v0 + e1 rounding of the traversal triangle and the
+// slab test's rounding).  Shared by K3a (leaf clusters of the quality pass) and K3b (refit), which therefore agree bit for bit.
+__device__ __forceinline__ Box3 leaf_box(const float v[9]) {
+    Box3 b;
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        const float lo = fminf(fminf(v[a], v[3 + a]), v[6 + a]), hi = fmaxf(fmaxf(v[a], v[3 + a]), v[6 + a]);
+        const float pad = 4.0e-7f * fmaxf(fabsf(lo), fabsf(hi)) + 1.0e-30f;
+        b.lo[a] = lo - pad; b.hi[a] = hi + pad;
+    }
+    return b;
+}
+
+// K3a: one thread per sorted leaf: gathers the face's FP64 inputs once, writes the 48-B triangle, the 64-B shading record and
+// the leaf's cluster box for the quality pass; also fills the collapse's queue with W4_EMPTY (saves a memset launch).
+__global__ void __launch_bounds__(256) emit_kernel(int n, const double* __restrict__ pos, const double* __restrict__ nrm,
+                                                   const double* __restrict__ uv, const int* __restrict__ mat_id,
+                                                   const int* __restrict__ leaf_face, TriGeom* __restrict__ tri,
+                                                   TriShade* __restrict__ shade, float4* __restrict__ cl_lo, float4* __restrict__ cl_hi,
+                                                   int* __restrict__ w4_queue) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
-    w4_queue[k] = -1;   // wide.cu's W4_EMPTY: the collapse's queue is prepared on the way (saves a memset launch)
+    w4_queue[k] = -1;
     const int f = leaf_face[k];
     const double* p = pos + 9 * (size_t)f;
     float v[9];
@@ -133,16 +144,25 @@ __global__ void __launch_bounds__(256) emit_refit_kernel(int n, const double* __
     s.c = make_float4((float)q[8], (float)t[0], (float)t[1], (float)t[2]);
     s.d = make_float4((float)t[3], (float)t[4], (float)t[5], 0.0f);
     shade[k] = s;
-
-    Box3 b;
-#pragma unroll
-    for (int a = 0; a < 3; a++) {
-        const float lo = fminf(fminf(v[a], v[3 + a]), v[6 + a]), hi = fmaxf(fmaxf(v[a], v[3 + a]), v[6 + a]);
-        const float pad = 4.0e-7f * fmaxf(fabsf(lo), fabsf(hi)) + 1.0e-30f;  // > 3 ulp: covers v0+e1 rounding and slab rounding
-        b.lo[a] = lo - pad; b.hi[a] = hi + pad;
-    }
+    const Box3 b = leaf_box(v);
     cl_lo[k] = make_float4(b.lo[0], b.lo[1], b.lo[2], __int_as_float(~k));   // leaf cluster of the quality pass (ploc.cu)
     cl_hi[k] = make_float4(b.hi[0], b.hi[1], b.hi[2], 0.0f);
+}
+
+// K3b: bottom-up AABB refit of the radix tree with atomic arrival counters.  One thread per sorted leaf forms the leaf box and
+// carries it up: at each parent the first child to arrive stores its box in the parent's slot and stops; the second one reads
+// the sibling's box back (L2) and continues with the union.  Runs on the build's SIDE stream next to the quality pass, which
+// needs only K3a's leaf boxes (lbvh_build); write_root: this tree is the one traversal walks, so its root box is the scene box.
+__global__ void __launch_bounds__(256) refit_kernel(int n, const double* __restrict__ pos, const int* __restrict__ leaf_face,
+                                                    const int* __restrict__ leaf_parent, BvhNode* nodes, unsigned* flags,
+                                                    float* __restrict__ root_box, const bool write_root) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const double* p = pos + 9 * (size_t)leaf_face[k];
+    float v[9];
+#pragma unroll
+    for (int a = 0; a < 9; a++) v[a] = __double2float_rn(p[a]);
+    Box3 b = leaf_box(v);
     if (n == 1) {  // degenerate tree: node 0 points at the only leaf twice
         store_child_box(&nodes[0], 0, b); store_child_box(&nodes[0], 1, b);
         int* c = reinterpret_cast<int*>(&nodes[0].q[3]);
@@ -169,7 +189,7 @@ __global__ void __launch_bounds__(256) emit_refit_kernel(int n, const double* __
         parent = c[2];
         if (parent < 0) break;
     }
-    for (int a = 0; a < 3; a++) { root_box[a] = b.lo[a]; root_box[3 + a] = b.hi[a]; }
+    if (write_root) for (int a = 0; a < 3; a++) { root_box[a] = b.lo[a]; root_box[3 + a] = b.hi[a]; }
 }
 
 // ---- K4: quantise the refitted nodes onto a 16-bit grid over the root box ----------------------------------
@@ -196,6 +216,49 @@ __global__ void __launch_bounds__(256) quantize_nodes_kernel(int n_nodes, const 
     qnodes[i] = out;
 }
 
+// ---- sort: one CTA for small scenes, CUB's device-wide onesweep otherwise ----------------------------------------------
+// cub::DeviceRadixSort is six launches (histogram, scan, four onesweep passes): 62 us for cornell-box's 15 056 keys, a sixth of
+// that build.  Up to 16 384 keys one CTA of 1024 threads sorts the (code, face) pairs in shared memory with
+// cub::BlockRadixSort — also an LSD radix sort, hence stable: ties keep face order, the canonical leaf order.
+#define BSORT_THREADS 1024
+#define BSORT_ITEMS 16
+typedef cub::BlockRadixSort<uint32_t, BSORT_THREADS, BSORT_ITEMS, int, 5> BlockSort;
+__global__ void __launch_bounds__(BSORT_THREADS) block_sort_kernel(const uint32_t* __restrict__ codes, int n, uint32_t* __restrict__ codes_sorted,
+                                                                   int* __restrict__ leaf_face) {
+    extern __shared__ __align__(16) unsigned char bsort_smem[];
+    BlockSort::TempStorage& temp = *reinterpret_cast<BlockSort::TempStorage*>(bsort_smem);
+    uint32_t key[BSORT_ITEMS]; int val[BSORT_ITEMS];
+#pragma unroll
+    for (int j = 0; j < BSORT_ITEMS; j++) {   // blocked arrangement: thread t holds items t*ITEMS .. (stability needs input order)
+        const int i = threadIdx.x * BSORT_ITEMS + j;
+        key[j] = i < n ? codes[i] : 0xFFFFFFFFu;   // padding sorts last (real codes have 30 bits)
+        val[j] = i;
+    }
+    BlockSort(temp).Sort(key, val, 0, 32);
+#pragma unroll
+    for (int j = 0; j < BSORT_ITEMS; j++) {
+        const int i = threadIdx.x * BSORT_ITEMS + j;
+        if (i < n) { codes_sorted[i] = key[j]; leaf_face[i] = val[j]; }
+    }
+}
+static int sort_codes(SceneBuffers& sb, cudaStream_t stream, int* nl) {
+    const int n = sb.n_faces;
+    if (n <= BSORT_THREADS * BSORT_ITEMS) {
+        static bool attr_set = false;   // per process; the attribute is per function and device-independent in value
+        const int smem = (int)sizeof(BlockSort::TempStorage);
+        cudaError_t e = cudaFuncSetAttribute(block_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return (int)e;
+        (void)attr_set;
+        block_sort_kernel<<<1, BSORT_THREADS, smem, stream>>>(sb.codes_obj, n, sb.codes_sorted, sb.leaf_face);
+        *nl += 1;
+        return (int)cudaGetLastError();
+    }
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(sb.cub_temp, sb.cub_temp_bytes, sb.codes_obj, sb.codes_sorted, sb.iota,
+                                                    sb.leaf_face, n, 0, 30, stream);
+    *nl += 6;
+    return (int)e;
+}
+
 // ---- host-side orchestration -----------------------------------------------------------------------
 size_t lbvh_sort_temp_bytes(int n) {
     size_t bytes = 0;
@@ -204,7 +267,10 @@ size_t lbvh_sort_temp_bytes(int n) {
     return bytes;
 }
 
-int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches) {
+// Two streams: the radix tree (K2) and its refit (K3b) need only the sorted codes; the quality pass needs only K3a's leaf boxes.
+// So after the sort the build forks: SIDE: K2 -> K3b;  MAIN: K3a -> PLOC rounds -> finish -> wide collapse; and joins at the
+// end (cornell-box: ~55 us of the radix tree's latency chain hidden behind ~150 us of clustering + collapse).
+int lbvh_build(SceneBuffers& sb, cudaStream_t stream, const BuildStreams& bs, int* launches) {
     const int n = sb.n_faces;
     const int tpb = 256;
     int nl = 0;
@@ -212,21 +278,25 @@ int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches) {
     if (e != cudaSuccess) return (int)e;
     morton_kernel<<<(n + tpb - 1) / tpb, tpb, 0, stream>>>(sb.pos, n, sb.codes_obj, sb.iota, sb.flags, sb.w4_ctr + 5); nl++;
     // stable LSD radix sort of (code, face index), 30 key bits: ties keep face-index order
-    e = cub::DeviceRadixSort::SortPairs(sb.cub_temp, sb.cub_temp_bytes, sb.codes_obj, sb.codes_sorted, sb.iota,
-                                        sb.leaf_face, n, 0, 30, stream);
-    if (e != cudaSuccess) return (int)e;
-    nl += 4;
-    if (n > 1) { radix_tree_kernel<<<(n - 1 + tpb - 1) / tpb, tpb, 0, stream>>>(sb.codes_sorted, n, sb.nodes, sb.leaf_parent); nl++; }
-    emit_refit_kernel<<<(n + tpb - 1) / tpb, tpb, 0, stream>>>(n, sb.pos, sb.nrm, sb.uv, sb.mat_id, sb.leaf_face, sb.leaf_parent,
-                                                               sb.nodes, sb.flags, sb.tri, sb.shade, sb.root_box, sb.cl_lo[0], sb.cl_hi[0], sb.w4_queue); nl++;
+    { const int se = sort_codes(sb, stream, &nl); if (se) return se; }
+    const bool ploc = sb.use_ploc && n >= 2;
+    if ((e = cudaEventRecord(bs.ev_fork, stream)) != cudaSuccess) return (int)e;
+    if ((e = cudaStreamWaitEvent(bs.side, bs.ev_fork, 0)) != cudaSuccess) return (int)e;
+    if (n > 1) { radix_tree_kernel<<<(n - 1 + tpb - 1) / tpb, tpb, 0, bs.side>>>(sb.codes_sorted, n, sb.nodes, sb.leaf_parent); nl++; }
+    refit_kernel<<<(n + tpb - 1) / tpb, tpb, 0, bs.side>>>(n, sb.pos, sb.leaf_face, sb.leaf_parent, sb.nodes, sb.flags, sb.root_box, !ploc); nl++;
+    if ((e = cudaEventRecord(bs.ev_join, bs.side)) != cudaSuccess) return (int)e;
+    emit_kernel<<<(n + tpb - 1) / tpb, tpb, 0, stream>>>(n, sb.pos, sb.nrm, sb.uv, sb.mat_id, sb.leaf_face, sb.tri, sb.shade,
+                                                         sb.cl_lo[0], sb.cl_hi[0], sb.w4_queue); nl++;
     const BvhNode* walk = sb.nodes;
     sb.root = 0; sb.walk_is_radix = true;
     bool w4_prepared = false;
-    if (sb.use_ploc && n >= 2) {
+    if (ploc) {
         const int pe = ploc_build(sb, stream, &nl, MCPT_WIDE != 0);
         if (pe) return pe;
         walk = sb.nodes2; sb.root = n - 2; sb.walk_is_radix = false;
         w4_prepared = MCPT_WIDE != 0;
+    } else {
+        if ((e = cudaStreamWaitEvent(stream, bs.ev_join, 0)) != cudaSuccess) return (int)e;   // the collapse walks the radix tree
     }
 #if MCPT_WIDE
     { const int we = wide_build(sb, walk, sb.root, stream, &nl, w4_prepared); if (we) return we; }
@@ -235,6 +305,7 @@ int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches) {
     const int n_nodes = n > 1 ? n - 1 : 1;
     quantize_nodes_kernel<<<(n_nodes + tpb - 1) / tpb, tpb, 0, stream>>>(n_nodes, walk, sb.root_box, sb.qnodes, sb.qgrid, sb.fold_pairs && n > 2); nl++;
 #endif
+    if (ploc && (e = cudaStreamWaitEvent(stream, bs.ev_join, 0)) != cudaSuccess) return (int)e;      // join
     if (launches) *launches = nl;
     sb.built = true;
     return (int)cudaGetLastError();

@@ -45,7 +45,9 @@ struct SceneBuffers {
 size_t lbvh_sort_temp_bytes(int n);
 // K1 Morton -> CUB radix sort -> K2 radix tree -> K3 leaf emit + atomic bottom-up refit -> K4 node quantisation.
 // Returns a cudaError_t as int; all work is enqueued on `stream`.
-int lbvh_build(SceneBuffers& sb, cudaStream_t stream, int* launches);
+// side: a second stream of the context, ev_fork / ev_join: timing-disabled events (the build forks after the sort, see lbvh.cu).
+struct BuildStreams { cudaStream_t side; cudaEvent_t ev_fork, ev_join; };
+int lbvh_build(SceneBuffers& sb, cudaStream_t stream, const BuildStreams& bs, int* launches);
 // Redo the wide collapse over the radix tree (quality pass stalled / too deep); enqueued on `stream`.
 int lbvh_fallback_to_radix(SceneBuffers& sb, cudaStream_t stream, int* launches);
 // K4a (ploc.cu): parallel locally-ordered clustering over the Morton-ordered leaf boxes -> sb.nodes2.

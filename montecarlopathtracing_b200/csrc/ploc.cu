@@ -24,7 +24,10 @@ namespace mcpt {
 #ifndef PLOC_RADIUS
 #define PLOC_RADIUS 8
 #endif
-#define PLOC_TPB 256
+#define PLOC_GRID_TPB 256      /* cooperative-grid variant of the rounds kernel */
+#define PLOC_CLUSTER_TPB 1024  /* one-cluster variant */
+#define PLOC_CLUSTER_CTAS 8
+#define PLOC_CLUSTER_MAX_N 65536
 #define PLOC_FINISH 1024
 #define PLOC_MAX_ITERS 4096
 
@@ -68,22 +71,30 @@ __device__ __forceinline__ void write_node(BvhNode* nodes, int id, const float4 
 // (Round 1 ran every round as four kernels + a CUB scan and synchronised with the host every fourth round to read the
 // cluster count: ~60 launches and three host round trips for cornell-box, 0.36 of the build's 0.60 ms.)  Every CTA owns a
 // contiguous range of the cluster array, so the order-preserving compaction needs only per-CTA counts:
-//   phase 1  per cluster: nearest neighbour j, and j's own nearest neighbour recomputed from the same shared-memory tile
-//            (halo 2 x RADIUS) — the mutual test needs no second pass; one flag byte per cluster (survives | merges-as-left |
-//            offset of j), per-CTA counts of survivors and merges                                     -> grid.sync
+//   phase 1  per cluster of a 256-cluster tile, and per cluster of its RADIUS-wide rims: nearest neighbour, into shared memory
+//            (boxes staged with a 2 x RADIUS halo) — the mutual test reads the partner's choice there, no second pass over
+//            global memory; one flag byte per cluster (survives | merges-as-left | offset of the partner), per-CTA counts of
+//            survivors and merges                                                                      -> grid.sync
 //   phase 2  every CTA sums the counts of the CTAs before it (and all of them: the next round's cluster count, identical
 //            in every CTA, no global state), scans its flags tile by tile and scatters survivors / writes the new nodes
 //            in array order — so node numbering does not depend on scheduling                          -> grid.sync
 #define PLOC_HALO (2 * PLOC_RADIUS)
 struct PlocState { int m; int node_base; int error; int rounds; };   // clusters alive, internal nodes created, stalled, rounds run
 
+// CLUSTER: the CTAs are ONE thread-block cluster (8 CTAs of 1024 threads) and the barrier is the hardware cluster barrier — a
+// fraction of a microsecond against ~3 us for a grid-wide barrier through L2; used up to 64 Ki triangles, where a round is
+// nothing but barrier latency (cornell-box: 7 rounds).  Otherwise: a cooperative grid that fills the GPU.
+template <int PLOC_TPB, bool CLUSTER>
 __global__ void __launch_bounds__(PLOC_TPB) ploc_rounds_kernel(PlocState* st, float4* lo0, float4* hi0, float4* lo1, float4* hi1,
                                                                unsigned char* __restrict__ flagb, uint2* blockcnt, BvhNode* __restrict__ nodes,
                                                                const int n) {
-    cg::grid_group grid = cg::this_grid();
+    auto all_ctas_sync = [] {
+        if (CLUSTER) cg::this_cluster().sync(); else cg::this_grid().sync();
+    };
     typedef cub::BlockScan<unsigned long long, PLOC_TPB> Scan;
     __shared__ typename Scan::TempStorage temp;
     __shared__ float4 slo[PLOC_TPB + 2 * PLOC_HALO], shi[PLOC_TPB + 2 * PLOC_HALO];
+    __shared__ int snn[PLOC_TPB + 2 * PLOC_RADIUS];
     __shared__ unsigned s_red[2][PLOC_TPB / 32];
     __shared__ unsigned long long s_pre[2];
     const int G = gridDim.x, b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -101,11 +112,20 @@ __global__ void __launch_bounds__(PLOC_TPB) ploc_rounds_kernel(PlocState* st, fl
                 if (g >= 0 && g < m) { slo[t] = lo[g]; shi[t] = hi[g]; }
             }
             __syncthreads();
+            // nearest neighbour of every cluster of the tile AND of the RADIUS clusters on either side (whose own neighbourhoods
+            // still lie inside the 2 x RADIUS halo): the mutual test then reads its partner's choice from shared memory
             const int i = base + tid;
+            if (i < m) snn[tid + PLOC_RADIUS] = ploc_nearest(slo, shi, tid + PLOC_HALO, i, m);
+            if (tid < 2 * PLOC_RADIUS) {
+                const int t = tid < PLOC_RADIUS ? tid : PLOC_TPB + tid;          // snn index: [0, R) left halo, [TPB+R, TPB+2R) right halo
+                const int g = base - PLOC_RADIUS + t;
+                if (g >= 0 && g < m) snn[t] = ploc_nearest(slo, shi, t + PLOC_RADIUS, g, m);
+            }
+            __syncthreads();
             bool survive = false, left = false;
             if (i < r1) {
-                const int j = ploc_nearest(slo, shi, tid + PLOC_HALO, i, m);
-                const bool mutual = j >= 0 && ploc_nearest(slo, shi, j - base + PLOC_HALO, j, m) == i;
+                const int j = snn[tid + PLOC_RADIUS];
+                const bool mutual = j >= 0 && snn[j - base + PLOC_RADIUS] == i;
                 survive = !(mutual && i > j); left = mutual && i < j;
                 flagb[i] = (unsigned char)((unsigned)survive | ((unsigned)left << 1) | ((unsigned)(j - i + PLOC_RADIUS) << 2));
             }
@@ -119,7 +139,7 @@ __global__ void __launch_bounds__(PLOC_TPB) ploc_rounds_kernel(PlocState* st, fl
             for (int w = 0; w < PLOC_TPB / 32; w++) { a += s_red[0][w]; c += s_red[1][w]; }
             blockcnt[b] = make_uint2(a, c);
         }
-        grid.sync();
+        all_ctas_sync();
         // ---- phase 2 ----
         unsigned long long before = 0ull, total = 0ull;   // packed (survivors << 32 | merges)
         for (int k = tid; k < G; k += PLOC_TPB) {
@@ -177,7 +197,7 @@ __global__ void __launch_bounds__(PLOC_TPB) ploc_rounds_kernel(PlocState* st, fl
         if (m_next >= m || rounds >= PLOC_MAX_ITERS) { error = 1; break; }   // no mutual pair (cannot happen on finite boxes) or runaway
         m = m_next;
         float4* t = lo; lo = lo_out; lo_out = t; t = hi; hi = hi_out; hi_out = t;
-        grid.sync();
+        all_ctas_sync();
     }
     if (b == 0 && tid == 0) { st->m = m; st->node_base = node_base; st->error = error; st->rounds = rounds | ((lo == lo0 ? 0 : 1) << 30); }
 }
@@ -186,12 +206,11 @@ __global__ void __launch_bounds__(PLOC_TPB) ploc_rounds_kernel(PlocState* st, fl
 __global__ void __launch_bounds__(PLOC_FINISH) ploc_finish_kernel(PlocState* st, const float4* __restrict__ lo0, const float4* __restrict__ hi0,
                                                                   const float4* __restrict__ lo1, const float4* __restrict__ hi1,
                                                                   BvhNode* __restrict__ nodes, float* __restrict__ root_box, unsigned* w4_ctr) {
-    typedef cub::BlockScan<unsigned long long, PLOC_FINISH> Scan;
-    __shared__ typename Scan::TempStorage temp;
     __shared__ float4 slo[PLOC_FINISH + 2 * PLOC_RADIUS], shi[PLOC_FINISH + 2 * PLOC_RADIUS];   // clusters at [RADIUS, RADIUS + m)
     __shared__ int snn[PLOC_FINISH];
-    __shared__ int s_m, s_base;
-    const int i = threadIdx.x;
+    __shared__ unsigned s_cnt[2][32];
+    const int i = threadIdx.x, lane = i & 31, warp = i >> 5;
+    const unsigned lt_mask = (1u << lane) - 1u;
     if (i == 0 && w4_ctr) { w4_ctr[0] = 1u; w4_ctr[1] = 0u; w4_ctr[2] = 0u; w4_ctr[3] = 0u; w4_ctr[4] = 0u; }   // wide.cu's W4_* counters
     int m = st->m, node_base = st->node_base;
     if (m > PLOC_FINISH || st->error) return;   // the rounds kernel stalled: mcpt_build_bvh falls back to the radix tree
@@ -216,24 +235,33 @@ __global__ void __launch_bounds__(PLOC_FINISH) ploc_finish_kernel(PlocState* st,
             survive = !(mutual && i > bj); left = mutual && i < bj;
             if (left) { blo = slo[bj + PLOC_RADIUS]; bhi = shi[bj + PLOC_RADIUS]; }
         }
-        const unsigned long long f = ((unsigned long long)survive << 32) | (unsigned long long)left;
-        unsigned long long s, total;
-        Scan(temp).ExclusiveSum(f, s, total);
-        __syncthreads();   // everyone has read slo/shi/snn; temp can be reused next round
+        // order-preserving compaction with warp ballots + one 32-wide shuffle scan of the per-warp counts (every warp does the
+        // same scan, so the totals need no broadcast): three barriers per round where a 1024-thread cub::BlockScan took six
+        const unsigned ms = __ballot_sync(0xffffffffu, survive), ml = __ballot_sync(0xffffffffu, left);
+        if (lane == 0) { s_cnt[0][warp] = (unsigned)__popc(ms); s_cnt[1][warp] = (unsigned)__popc(ml); }
+        __syncthreads();   // everyone has read slo/shi/snn; the counts are in
+        unsigned cs = s_cnt[0][lane], cl = s_cnt[1][lane];
+        unsigned is = cs, il = cl;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned vs = __shfl_up_sync(0xffffffffu, is, d), vl = __shfl_up_sync(0xffffffffu, il, d);
+            if (lane >= d) { is += vs; il += vl; }
+        }
+        const int total_s = (int)__shfl_sync(0xffffffffu, is, 31), total_l = (int)__shfl_sync(0xffffffffu, il, 31);
+        const int off_s = (int)__shfl_sync(0xffffffffu, is - cs, warp), off_l = (int)__shfl_sync(0xffffffffu, il - cl, warp);
         if (survive) {
-            const int pos = (int)(s >> 32);
+            const int pos = off_s + __popc(ms & lt_mask);
             if (left) {
-                const int id = node_base + (int)(s & 0xffffffffull);
+                const int id = node_base + off_l + __popc(ml & lt_mask);
                 write_node(nodes, id, alo, ahi, blo, bhi);
                 alo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), __int_as_float(id));
                 ahi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.0f);
             }
             slo[pos + PLOC_RADIUS] = alo; shi[pos + PLOC_RADIUS] = ahi;
         }
-        if (i == 0) { s_m = (int)(total >> 32); s_base = node_base + (int)(total & 0xffffffffull); }
         __syncthreads();
-        if (s_m >= m || ++rounds > PLOC_MAX_ITERS) { if (i == 0) st->error = 1; return; }
-        m = s_m; node_base = s_base;
+        if (total_s >= m || ++rounds > PLOC_MAX_ITERS) { if (i == 0) st->error = 1; return; }
+        m = total_s; node_base += total_l;
     }
     if (i == 0) {
         st->m = m; st->node_base = node_base;
@@ -256,21 +284,32 @@ int ploc_build(SceneBuffers& sb, cudaStream_t stream, int* launches, bool init_w
     if (n < 2) return 0;
     cudaError_t e;
     PlocState* st = (PlocState*)sb.ploc_state;
-    if (!sb.ploc_resident_blocks) {
-        int dev = 0, sms = 0, per_sm = 0, coop = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ploc_rounds_kernel, PLOC_TPB, 0);
-        if (e != cudaSuccess || sms <= 0 || per_sm <= 0 || !coop) return (int)(e != cudaSuccess ? e : cudaErrorInvalidConfiguration);
-        sb.ploc_resident_blocks = min(sms * per_sm, 4096);
-    }
-    int blocks = min(sb.ploc_resident_blocks, (n + PLOC_TPB - 1) / PLOC_TPB);
     float4 *lo0 = sb.cl_lo[0], *hi0 = sb.cl_hi[0], *lo1 = sb.cl_lo[1], *hi1 = sb.cl_hi[1];
-    unsigned char* flagb = (unsigned char*)sb.ploc_flag; uint2* blockcnt = (uint2*)sb.ploc_temp; BvhNode* nodes = sb.nodes2; int nn = n;
-    void* args[] = {(void*)&st, (void*)&lo0, (void*)&hi0, (void*)&lo1, (void*)&hi1, (void*)&flagb, (void*)&blockcnt, (void*)&nodes, (void*)&nn};
-    e = cudaLaunchCooperativeKernel((const void*)ploc_rounds_kernel, dim3(blocks), dim3(PLOC_TPB), args, 0, stream);
-    if (e != cudaSuccess) return (int)e;
+    unsigned char* flagb = sb.ploc_flag; uint2* blockcnt = (uint2*)sb.ploc_temp; BvhNode* nodes = sb.nodes2; int nn = n;
+    if (n <= PLOC_CLUSTER_MAX_N) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(PLOC_CLUSTER_CTAS); cfg.blockDim = dim3(PLOC_CLUSTER_TPB); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = PLOC_CLUSTER_CTAS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        e = cudaLaunchKernelEx(&cfg, ploc_rounds_kernel<PLOC_CLUSTER_TPB, true>, st, lo0, hi0, lo1, hi1, flagb, blockcnt, nodes, nn);
+        if (e != cudaSuccess) return (int)e;
+    } else {
+        if (!sb.ploc_resident_blocks) {
+            int dev = 0, sms = 0, per_sm = 0, coop = 0;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ploc_rounds_kernel<PLOC_GRID_TPB, false>, PLOC_GRID_TPB, 0);
+            if (e != cudaSuccess || sms <= 0 || per_sm <= 0 || !coop) return (int)(e != cudaSuccess ? e : cudaErrorInvalidConfiguration);
+            sb.ploc_resident_blocks = min(sms * per_sm, 4096);
+        }
+        int blocks = min(sb.ploc_resident_blocks, (n + PLOC_GRID_TPB - 1) / PLOC_GRID_TPB);
+        void* args[] = {(void*)&st, (void*)&lo0, (void*)&hi0, (void*)&lo1, (void*)&hi1, (void*)&flagb, (void*)&blockcnt, (void*)&nodes, (void*)&nn};
+        e = cudaLaunchCooperativeKernel((const void*)ploc_rounds_kernel<PLOC_GRID_TPB, false>, dim3(blocks), dim3(PLOC_GRID_TPB), args, 0, stream);
+        if (e != cudaSuccess) return (int)e;
+    }
     ploc_finish_kernel<<<1, PLOC_FINISH, 0, stream>>>(st, lo0, hi0, lo1, hi1, sb.nodes2, sb.root_box, init_w4 ? sb.w4_ctr : nullptr);
     if (launches) *launches += 2;
     return (int)cudaGetLastError();

@@ -14,8 +14,11 @@
 // with __nanosleep when nothing arrived, and the wait is bounded (error flag instead of a hang).
 // The layout is breadth-first, so the top of the tree is contiguous; which sibling subtree gets the lower index depends on
 // the order of the atomics, the TREE (and therefore every traversal result) does not.
+#include <cooperative_groups.h>
 #include "lbvh.h"
 #include "quant.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace mcpt {
 
@@ -135,6 +138,87 @@ __global__ void __launch_bounds__(256) wide_collapse_kernel(const BvhNode* __res
     if (lane == 0 && deepest) atomicMax(&ctr[W4_LEVELS], deepest);
 }
 
+
+// ---- small trees: ONE thread-block cluster, level by level ---------------------------------------------------------------
+// Below ~64 Ki triangles the kernel above is nothing but a latency chain: a level's nodes are found by POLLING the queue through
+// L2, one level after the other (cornell-box: 118 us for 6 300 wide nodes in ~10 levels).  Here the 8 CTAs of one cluster take a
+// whole level at a time — its entries are the queue slots [begin, end) — and meet at the hardware cluster barrier (two per
+// level: one so that every CTA sees the level's queue entries and tail, one so that nobody moves the tail before all have read
+// it).  Same collapse rule, same tree; sibling numbering again depends on the order of the atomics only.
+#define W4_SMALL_CTAS 8
+#define W4_SMALL_TPB 512
+#define W4_SMALL_MAX_N 65536
+__global__ void __launch_bounds__(W4_SMALL_TPB) wide_collapse_small_kernel(const BvhNode* __restrict__ nodes, const int root2, const int max_nodes,
+                                                                           const float* __restrict__ root_box, QNode4* __restrict__ out,
+                                                                           int* queue, unsigned* ctr, const bool fold, QGrid* __restrict__ qgrid) {
+    cg::cluster_group cluster = cg::this_cluster();
+    const int nthreads = W4_SMALL_CTAS * W4_SMALL_TPB, gtid = blockIdx.x * W4_SMALL_TPB + threadIdx.x, lane = threadIdx.x & 31;
+    float o[3], cell[3], inv[3];
+    quant_grid(root_box, o, cell, inv);
+    if (gtid == 0) {
+        qgrid->origin = make_float4(o[0], o[1], o[2], 0.0f);
+        qgrid->cell = make_float4(cell[0], cell[1], cell[2], 0.0f);
+    }
+    int begin = 0, end = 1;
+    unsigned levels = 0;
+    __shared__ int s_end;
+    while (begin < end && end <= max_nodes) {
+        for (int base = begin + (gtid - lane); base < end; base += nthreads) {   // warp-uniform trip count
+            const int t = base + lane;
+            const bool active = t < end;
+            W4Slot s[4];
+            int cnt = 0, m = 0;
+            if (active) {
+                const int id = t == 0 ? root2 : __ldcg(&queue[t]);
+                cnt = 2;
+                w4_children(nodes, id, fold, s[0], s[1]);
+                for (int step = 0; step < 2; step++) {
+                    int pick = -1; float best = -1.0f;
+                    for (int j = 0; j < cnt; j++) {
+                        const float a = w4_area(s[j]);
+                        if (s[j].ref >= 0 && a > best) { best = a; pick = j; }
+                    }
+                    if (pick < 0) break;
+                    const int open = s[pick].ref;
+                    w4_children(nodes, open, fold, s[pick], s[cnt]);
+                    cnt++;
+                }
+                for (int j = 0; j < cnt; j++) m += s[j].ref >= 0;
+            }
+            int incl = m;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
+            const int total = __shfl_sync(0xffffffffu, incl, 31);
+            unsigned at = 0;
+            if (lane == 0 && total) at = atomicAdd(&ctr[W4_TAIL], (unsigned)total);
+            at = __shfl_sync(0xffffffffu, at, 0) + (unsigned)(incl - m);
+            if (active) {
+                QNode4 q;
+                int k = 0;
+                for (int j = 0; j < 4; j++) {
+                    if (j < cnt) {
+                        int ref = s[j].ref;
+                        if (ref >= 0) { const int w = (int)at + k++; __stcg(&queue[w], ref); ref = w; }
+                        q.c[j] = make_uint4(quant_lo(s[j].lo[0], o[0], inv[0]) | (quant_hi(s[j].hi[0], o[0], inv[0]) << 16),
+                                            quant_lo(s[j].lo[1], o[1], inv[1]) | (quant_hi(s[j].hi[1], o[1], inv[1]) << 16),
+                                            quant_lo(s[j].lo[2], o[2], inv[2]) | (quant_hi(s[j].hi[2], o[2], inv[2]) << 16), (unsigned)ref);
+                    } else {
+                        q.c[j] = make_uint4(0x0000FFFFu, 0x0000FFFFu, 0x0000FFFFu, 0x80000000u);   // inverted box: never hit
+                    }
+                }
+                out[t] = q;
+            }
+        }
+        levels++;
+        cluster.sync();                                   // the level's queue entries and tail reservations are complete
+        if (threadIdx.x == 0) s_end = (int)__ldcg(&ctr[W4_TAIL]);
+        __syncthreads();
+        begin = end; end = s_end;
+        cluster.sync();                                   // everybody has read the tail before the next level moves it
+    }
+    if (gtid == 0) { ctr[W4_PROCESSED] = (unsigned)end; ctr[W4_LEVELS] = levels; ctr[W4_ERROR] = end > max_nodes ? 1u : 0u; ctr[W4_FINISHED] = 1u; }
+}
+
 int wide_build(SceneBuffers& sb, const BvhNode* walk, int root2, cudaStream_t stream, int* launches, bool prepared) {
     const int n = sb.n_faces;
     const int max_nodes = n > 1 ? n - 1 : 1;
@@ -144,6 +228,19 @@ int wide_build(SceneBuffers& sb, const BvhNode* walk, int root2, cudaStream_t st
         if (e != cudaSuccess) return (int)e;
         wide_init_kernel<<<1, 1, 0, stream>>>(sb.w4_ctr);
         if (launches) *launches += 2;
+    }
+    if (max_nodes <= W4_SMALL_MAX_N) {   // one cluster, level by level
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(W4_SMALL_CTAS); cfg.blockDim = dim3(W4_SMALL_TPB); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = W4_SMALL_CTAS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        const bool fold_s = sb.fold_pairs && n > 2;
+        e = cudaLaunchKernelEx(&cfg, wide_collapse_small_kernel, walk, root2, max_nodes, (const float*)sb.root_box, sb.qnodes4, sb.w4_queue,
+                               sb.w4_ctr, fold_s, sb.qgrid);
+        if (launches) *launches += 1;
+        return (int)(e != cudaSuccess ? e : cudaGetLastError());
     }
     // a fully RESIDENT grid (the no-deadlock argument needs every thread to be running): launched COOPERATIVELY, so the runtime
     // refuses the launch instead of letting CTAs wait for SMs that another context or stream holds; the grid size comes from

@@ -4,6 +4,7 @@
   python tools/ncu_summary.py metrics <report.ncu-rep> <out.md>    key counters of every profiled launch in a --set full report
   python tools/ncu_summary.py source <report.ncu-rep> <out.md>     per-instruction execution counts of the first launch (source
                                                                    view): share and active lanes per 20-instruction segment, opcode mix
+  python tools/ncu_summary.py lines <report.ncu-rep> <out.md>      the same per CUDA source line (top lines by instructions + stall samples)
 """
 import collections
 import csv
@@ -96,5 +97,39 @@ def source(src, dst, seg=20):
             f.write("| %d-%d | %.1f %% | %.1f | %d | `%s` |\n" % (k, k + len(g) - 1, 100 * e / tot, sum(d[2] for d in g) / max(e, 1), sum(d[3] for d in g), g[0][0][:48]))
 
 
+def lines(src, dst, top=45):
+    """Per CUDA source line (needs -lineinfo and --import-source on): executed warp instructions, active lanes, stall samples."""
+    raw = subprocess.run(["ncu", "-i", src, "--page", "source", "--csv", "--print-source", "cuda,sass"], stdout=subprocess.PIPE, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    per, fname, hdr, kernel = [], "?", None, "?"
+    for r in rows:
+        if not r:
+            continue
+        if r[0] == "File Path":
+            fname = r[1].split("/")[-1]
+        elif r[0] == "Function Name":
+            kernel = r[1]
+        elif r[0] == "Line No":
+            hdr = r
+        elif hdr and r[0].isdigit() and len(r) > 8 and r[2] == "-":
+            d = dict(zip(hdr[4:], r[4:]))
+            try:
+                per.append((fname, int(r[0]), r[1].strip(), int(d["Instructions Executed"] or 0), int(d["Thread Instructions Executed"] or 0), int(d["# Samples"] or 0)))
+            except (KeyError, ValueError):
+                pass
+    tot = sum(p[3] for p in per) or 1
+    smp = sum(p[5] for p in per) or 1
+    byfile = collections.Counter()
+    for p in per:
+        byfile[p[0]] += p[3]
+    with open(dst, "w") as f:
+        f.write("# ncu source view by CUDA line\n\nSource: `%s`, `%s`: %d warp instructions executed, %.1f active lanes per instruction, %d stall samples.\n\n" %
+                (src, short(kernel), tot, sum(p[4] for p in per) / tot, smp))
+        f.write("Share of executed warp instructions by file: " + ", ".join("%s %.1f %%" % (k, 100 * v / tot) for k, v in byfile.most_common()) + "\n\n")
+        f.write("| file:line | inst share | lanes | sample share | source |\n|---|---:|---:|---:|---|\n")
+        for p in sorted(per, key=lambda p: -(p[3] / tot + p[5] / smp))[:top]:
+            f.write("| %s:%d | %.1f %% | %.1f | %.1f %% | `%s` |\n" % (p[0], p[1], 100 * p[3] / tot, p[4] / max(p[3], 1), 100 * p[5] / smp, p[2][:90].replace("|", "¦")))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "metrics": metrics, "source": source}[sys.argv[1]](sys.argv[2], sys.argv[3])
+    {"launches": launches, "metrics": metrics, "source": source, "lines": lines}[sys.argv[1]](sys.argv[2], sys.argv[3])
