@@ -107,7 +107,13 @@ typedef struct mcpt_stats {
 enum { MCPT_MODE_MEGAKERNEL = 0, MCPT_MODE_WAVEFRONT = 1 };
 enum { MCPT_FLAG_COUNT = 1,            /* count node visits / triangle tests (slower) */
        MCPT_FLAG_NO_PRIMARY_REUSE = 2, /* re-trace the (identical, Q4) primary ray for every sample */
-       MCPT_FLAG_NO_SHADOW_EARLY_OUT = 4 /* walk every shadow ray to its closest hit even after its answer is settled (same image, bit for bit) */ };
+       MCPT_FLAG_NO_SHADOW_EARLY_OUT = 4, /* walk every shadow ray to its closest hit even after its answer is settled (same image, bit for bit) */
+       /* Quality extensions.  OFF by default: with either of them the image is no longer the reference's. */
+       MCPT_FLAG_JITTER = 8,          /* every sample's primary ray goes through its own Philox-drawn point of the pixel (the reference
+                                         shoots all samples through the pixel's corner, MTPC/pathTracing.cpp:305-308): anti-aliasing */
+       MCPT_FLAG_ANYHIT_SHADOW = 16   /* a light sample is visible iff NOTHING lies between the shading point and it (the reference:
+                                         iff the closest hit carries the light's material, MTPC/pathTracing.cpp:212-215, so the
+                                         far side of a convex light counts as visible through its near side) */ };
 
 /* Number of sample chunks a render is always cut into (chunk k = samples [k*spp/C, (k+1)*spp/C)); GPU r of R in
  * {1,2,4,8} owns chunks [r*C/R,(r+1)*C/R).  Every chunk is accumulated sequentially into its own plane and the planes are

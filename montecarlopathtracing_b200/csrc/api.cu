@@ -60,6 +60,7 @@ DeviceScene device_scene(const mcpt_ctx* c) {
     DeviceScene d{};
     d.n_faces = c->sb.n_faces; d.n_materials = c->n_materials; d.n_textures = c->n_textures; d.n_lights = c->n_lights;
     d.root = MCPT_WIDE ? 0 : c->sb.root; d.qnodes4 = c->sb.qnodes4; d.area0 = c->area0;
+    d.n_wide = c->sb.n_wide; d.wide_levels = c->sb.wide_levels;
     d.nodes = c->sb.nodes; d.qnodes = c->sb.qnodes; d.qgrid = c->sb.qgrid; d.tri = c->sb.tri; d.shade = c->sb.shade; d.leaf_face = c->sb.leaf_face; d.pos = c->sb.pos;
     d.materials = c->d_materials; d.textures = c->d_textures; d.tex_bytes = c->d_tex_bytes;
     d.lights = c->d_lights; d.light_tris = c->d_light_tris; d.light_cdf = c->d_light_cdf;
@@ -513,6 +514,7 @@ MCPT_API int mcpt_build_bvh(mcpt_ctx* c, float* ms_out) {
     CU(cudaEventElapsedTime(&c->last_build_ms, c->ev0, c->ev1));
     if (ms_out) *ms_out = c->last_build_ms;
     c->last_build_launches = launches;
+    c->sb.n_wide = (int)w4[0]; c->sb.wide_levels = (int)w4[4];
 #if MCPT_WIDE
     if (wide_bad()) { c->sb.built = false; return fail_cuda(cudaErrorLaunchTimeout, "wide_build: the breadth-first collapse did not finish"); }
     if (too_deep()) {
@@ -605,6 +607,7 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
                    int* launches) {
     if (mode != MCPT_MODE_MEGAKERNEL && mode != MCPT_MODE_WAVEFRONT) return fail_arg("render: unknown mode");
     if (getenv("MCPT_NO_SHADOW_EARLY_OUT")) flags |= MCPT_FLAG_NO_SHADOW_EARLY_OUT;   // developer A/B switch (same image either way)
+    if (flags & MCPT_FLAG_JITTER) flags |= MCPT_FLAG_NO_PRIMARY_REUSE;                  // every sample has its own primary ray
     const int nch = ce - cb;
     const size_t plane = (size_t)width * height * 3;
     CU(grow(c->d_planes, c->planes_cap, sizeof(float) * plane * nch));
@@ -632,6 +635,9 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
     }
     while (g > 1 && (long long)width * height * (nch / g) < want) g >>= 1;
     P.chunks_per_thread = g;
+    P.flags = flags;
+    P.div_tiles_x = make_fastdiv((unsigned)((width + 7) >> 3));
+    P.div_tiles = make_fastdiv((unsigned)(((width + 7) >> 3) * ((height + 3) >> 2)));
     P.seed_lo = (unsigned)c->seed; P.seed_hi = (unsigned)(c->seed >> 32);
     P.planes = c->d_planes; P.counters = c->d_counters;
     CU(cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));

@@ -66,6 +66,7 @@ struct DeviceScene {
     int n_faces;
     int n_materials, n_textures, n_lights;
     int root;                 // >= 0 internal node, < 0 leaf (single-triangle scene)
+    int n_wide, wide_levels;  // wide nodes in use; internal levels of the wide tree (<= MCPT_MAX_WIDE_LEVELS)
     float area0;              // area of light 0: the frozen range of the selection uniform (quirk Q6)
     const BvhNode* nodes;     // FP32 nodes (build product, structural tests)
     const QNode* qnodes;      // 16-bit quantised nodes (what traversal reads)
@@ -89,6 +90,27 @@ struct DCamera {
     int width, height;
 };
 
+// n / d for 32-bit unsigned n and a divisor known on the host (Granlund-Montgomery round-up multiplier, branch-free form):
+// four integer instructions instead of the ~20 of a division by a kernel parameter (wf_shade maps slot -> tile -> pixel with four).
+struct FastDiv { unsigned mul, shift, d; };
+inline FastDiv make_fastdiv(unsigned d) {
+    FastDiv f; f.d = d;
+    if (d <= 1u) { f.mul = 0u; f.shift = 0u; return f; }   // handled by the d == 1 branch of fastdiv
+    unsigned s = 0; while ((1ull << s) < d) s++;             // ceil(log2 d)
+    f.mul = (unsigned)((((1ull << s) - d) << 32) / d + 1ull);
+    f.shift = s - 1u;
+    return f;
+}
+__host__ __device__ __forceinline__ unsigned fastdiv(unsigned n, const FastDiv f) {
+    if (f.d <= 1u) return n;
+#ifdef __CUDA_ARCH__
+    const unsigned q = __umulhi(f.mul, n);
+#else
+    const unsigned q = (unsigned)(((unsigned long long)f.mul * n) >> 32);
+#endif
+    return (((n - q) >> 1) + q) >> f.shift;
+}
+
 struct RenderParams {
     DeviceScene scene;
     DCamera cam;
@@ -96,6 +118,8 @@ struct RenderParams {
     int chunk_begin;    // first sample chunk rendered by this launch
     int n_chunks;       // chunks rendered by this launch
     int chunks_per_thread;
+    FastDiv div_tiles, div_tiles_x;   // by the number of 8x4 pixel tiles, by the tiles per row
+    int flags;                        // MCPT_FLAG_* of the render (the quality extensions are run-time switches)
     unsigned seed_lo, seed_hi;
     const float* cam_dirs; // height*width*3: primary ray directions from raygen_kernel (K7)
     float* planes;      // n_chunks planes of height*width*3 floats: per-chunk SUM of sample radiance

@@ -3,7 +3,6 @@
 // MTPC/sceneManagement.cpp:311-314) and the balanced-tree BVH (MTPC/BVH.cpp:44-132).
 // This file is compiled WITHOUT fused multiply-add (--fmad=false, see build.py): K1's float pipeline
 // must be IEEE-identical to the host's.
-#include <cub/block/block_radix_sort.cuh>
 #include <cub/device/device_radix_sort.cuh>
 #include "lbvh.h"
 #include "quant.cuh"
@@ -216,46 +215,15 @@ __global__ void __launch_bounds__(256) quantize_nodes_kernel(int n_nodes, const 
     qnodes[i] = out;
 }
 
-// ---- sort: one CTA for small scenes, CUB's device-wide onesweep otherwise ----------------------------------------------
-// cub::DeviceRadixSort is six launches (histogram, scan, four onesweep passes): 62 us for cornell-box's 15 056 keys, a sixth of
-// that build.  Up to 16 384 keys one CTA of 1024 threads sorts the (code, face) pairs in shared memory with
-// cub::BlockRadixSort — also an LSD radix sort, hence stable: ties keep face order, the canonical leaf order.
-#define BSORT_THREADS 1024
-#define BSORT_ITEMS 16
-typedef cub::BlockRadixSort<uint32_t, BSORT_THREADS, BSORT_ITEMS, int, 5> BlockSort;
-__global__ void __launch_bounds__(BSORT_THREADS) block_sort_kernel(const uint32_t* __restrict__ codes, int n, uint32_t* __restrict__ codes_sorted,
-                                                                   int* __restrict__ leaf_face) {
-    extern __shared__ __align__(16) unsigned char bsort_smem[];
-    BlockSort::TempStorage& temp = *reinterpret_cast<BlockSort::TempStorage*>(bsort_smem);
-    uint32_t key[BSORT_ITEMS]; int val[BSORT_ITEMS];
-#pragma unroll
-    for (int j = 0; j < BSORT_ITEMS; j++) {   // blocked arrangement: thread t holds items t*ITEMS .. (stability needs input order)
-        const int i = threadIdx.x * BSORT_ITEMS + j;
-        key[j] = i < n ? codes[i] : 0xFFFFFFFFu;   // padding sorts last (real codes have 30 bits)
-        val[j] = i;
-    }
-    BlockSort(temp).Sort(key, val, 0, 32);
-#pragma unroll
-    for (int j = 0; j < BSORT_ITEMS; j++) {
-        const int i = threadIdx.x * BSORT_ITEMS + j;
-        if (i < n) { codes_sorted[i] = key[j]; leaf_face[i] = val[j]; }
-    }
-}
+// ---- sort ------------------------------------------------------------------------------------------------------------
+// cub::DeviceRadixSort::SortPairs over 30 key bits (a single-tile kernel below ~4.8 k keys, histogram + scan + four onesweep
+// passes above): LSD, hence stable — ties keep face order, the canonical leaf order.  Measured and dropped: one CTA of 1024
+// threads x 16 keys with cub::BlockRadixSort for up to 16 Ki keys (70.8 us for cornell-box's 15 056 keys against 62 us here).
 static int sort_codes(SceneBuffers& sb, cudaStream_t stream, int* nl) {
     const int n = sb.n_faces;
-    if (n <= BSORT_THREADS * BSORT_ITEMS) {
-        static bool attr_set = false;   // per process; the attribute is per function and device-independent in value
-        const int smem = (int)sizeof(BlockSort::TempStorage);
-        cudaError_t e = cudaFuncSetAttribute(block_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return (int)e;
-        (void)attr_set;
-        block_sort_kernel<<<1, BSORT_THREADS, smem, stream>>>(sb.codes_obj, n, sb.codes_sorted, sb.leaf_face);
-        *nl += 1;
-        return (int)cudaGetLastError();
-    }
     cudaError_t e = cub::DeviceRadixSort::SortPairs(sb.cub_temp, sb.cub_temp_bytes, sb.codes_obj, sb.codes_sorted, sb.iota,
                                                     sb.leaf_face, n, 0, 30, stream);
-    *nl += 6;
+    *nl += n <= 4864 ? 1 : 6;
     return (int)e;
 }
 

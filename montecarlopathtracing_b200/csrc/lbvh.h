@@ -37,6 +37,7 @@ struct SceneBuffers {
     int ploc_resident_blocks = 0;      // co-resident CTAs of ploc_rounds_kernel on this context's device
     bool walk_is_radix = false;        // the traversal tree is the radix tree (MCPT_BVH=lbvh, or the quality pass fell back)
     int root = 0;                      // root of the traversal tree (0: radix tree, n-2: PLOC tree)
+    int n_wide = 0, wide_levels = 0;   // wide nodes in use / internal levels of the wide tree (read back by mcpt_build_bvh)
     void* arena = nullptr;             // every pointer above is carved from this one allocation (api.cu alloc_scene)
     bool built = false;
 };

@@ -6,7 +6,7 @@
 
 namespace mcpt {
 
-enum { STREAM_PATH = 0, STREAM_FRESNEL = 1, STREAM_LIGHT0 = 2 };
+enum { STREAM_PATH = 0, STREAM_FRESNEL = 1, STREAM_LIGHT0 = 2, STREAM_JITTER = 0x7FFFFFFF };   // LIGHT0 + l for light l
 
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
 #pragma unroll

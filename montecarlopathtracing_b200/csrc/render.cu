@@ -6,6 +6,7 @@
 // centroid-biased light points (Q7), the double receiver cosine and max(1,d) clamp (Q8), lobe
 // pick without pdf division (Q9).
 #include "render.h"
+#include "exact.cuh"
 #include "shade.cuh"
 
 namespace mcpt {
@@ -48,7 +49,7 @@ int launch_raygen(const DCamera& cam, float* d_dirs, cudaStream_t stream) {
 enum { PH_PRIMARY = -2, PH_NEWSAMPLE = -1 };
 
 template <bool COUNT, bool REUSE_PRIMARY>
-__global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P, const bool early_out) {
+__global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
     const DeviceScene& sc = P.scene;
     const int W = P.cam.width, H = P.cam.height;
     const int tiles_x = (W + 7) >> 3, tiles_y = (H + 3) >> 2, n_tiles = tiles_x * tiles_y;
@@ -67,6 +68,9 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P, const
                                 __ldg(P.cam_dirs + 3 * (size_t)pixel + 2));
         const float3 cam_o = f3((float)P.cam.eye[0], (float)P.cam.eye[1], (float)P.cam.eye[2]);
         const int nl = sc.n_lights;
+        const bool jitter = (P.flags & MCPT_FLAG_JITTER) != 0, anyhit = (P.flags & MCPT_FLAG_ANYHIT_SHADOW) != 0;
+        const bool early_out = !(P.flags & MCPT_FLAG_NO_SHADOW_EARLY_OUT);
+        float3 prim_d = cam_d;                                          // this sample's primary direction (differs per sample with jitter)
         int chunk = P.chunk_begin + group * P.chunks_per_thread;       // global chunk index
         const int chunk_end = chunk + P.chunks_per_thread;
         int s = (int)((long long)chunk * P.spp / MCPT_NUM_CHUNKS);
@@ -74,7 +78,7 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P, const
         float3 sum = f3(0.f, 0.f, 0.f);
         Hit hit0; hit0.k = -1; hit0.t = 0.f; hit0.u = 0.f; hit0.v = 0.f;
         bool have_hit0 = false;
-        PathVertex vx; vx.mat = 0; vx.p = vx.pn = vx.kd = vx.wo = f3(0.f, 0.f, 0.f);
+        PathVertex vx; vx.mat = 0; vx.k = 0; vx.t = 0.f; vx.p = vx.pn = vx.kd = vx.wo = f3(0.f, 0.f, 0.f);
         float3 beta = f3(1.f, 1.f, 1.f), L = f3(0.f, 0.f, 0.f), pend = f3(0.f, 0.f, 0.f), wnext = f3(1.f, 1.f, 1.f);
         float3 ro = cam_o, rd = cam_d; float rtmax = 3.0e38f;
         int phase = PH_NEWSAMPLE, lobe = LOBE_DIFFUSE, light_mat = -1;
@@ -89,7 +93,7 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P, const
             const int m = __float_as_int(__ldg(&sc.tri[h.k].v0m).w);
             const int li = sc.materials[m].light_id;
             if (li >= 0) { finish_sample(f3(sc.lights[li].radiance[0], sc.lights[li].radiance[1], sc.lights[li].radiance[2])); return; }
-            make_vertex(sc, h, cam_d, vx);
+            make_vertex(sc, h, prim_d, vx);
             beta = f3(1.f, 1.f, 1.f); L = f3(0.f, 0.f, 0.f); bounce = 0; phase = 0;
         };
 
@@ -107,11 +111,14 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P, const
                     }
                     if (chunk >= chunk_end) { done = true; break; }
                     if (REUSE_PRIMARY && have_hit0) begin_path(hit0);   // identical primary ray (quirk Q4): reuse its hit
-                    else { phase = PH_PRIMARY; ro = cam_o; rd = cam_d; rtmax = 3.0e38f; have_ray = true; }
+                    else {
+                        if (jitter) prim_d = jittered_primary_dir(P.cam, x, y, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
+                        phase = PH_PRIMARY; ro = cam_o; rd = prim_d; rtmax = 3.0e38f; have_ray = true;
+                    }
                 } else if (phase < nl) {
                     const float4 u = philox_uniform4(bounce, STREAM_LIGHT0 + phase, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
                     const DLight& Lt = sc.lights[phase];
-                    if (sample_light(sc, Lt, vx, u, ro, rd, rtmax, pend)) { light_mat = Lt.mat_id; have_ray = true; }
+                    if (sample_light(sc, Lt, vx, u, ro, rd, rtmax, pend, anyhit)) { light_mat = Lt.mat_id; have_ray = true; }
                     else phase++;
                 } else {
                     const float4 u = philox_uniform4(bounce, STREAM_PATH, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
@@ -125,7 +132,11 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P, const
             if (done) break;
             // ---- the single traversal site ----
             n_rays++;
-            const Occluder oc = (early_out && phase >= 0 && phase < nl) ? shadow_occluder(sc.lights[phase], ro, rd, rtmax) : no_occluder();
+            Occluder oc = no_occluder();
+            if (phase >= 0 && phase < nl) {
+                if (anyhit) { oc.t = 3.0e38f; oc.light_mat = -2; }   // any hit settles it
+                else if (early_out) oc = shadow_occluder(sc.lights[phase], ro, rd, rtmax);
+            }
             const Hit h = trace_closest<COUNT>(sc, ro, rd, rtmax, n_nodes, n_tris, oc);
             // ---- consume the result ----
             if (phase == PH_PRIMARY) {
@@ -133,7 +144,8 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P, const
                 begin_path(h);
             } else if (phase < nl) {
                 // visible iff the CLOSEST hit carries the light's material (:212-215)
-                if (h.k >= 0 && __float_as_int(__ldg(&sc.tri[h.k].v0m).w) == light_mat) L = add_rn(L, mul_rn(beta, pend));
+                const bool visible = anyhit ? h.k < 0 : (h.k >= 0 && __float_as_int(__ldg(&sc.tri[h.k].v0m).w) == light_mat);
+                if (visible) L = add_rn(L, mul_rn(beta, pend));
                 phase++;
             } else {
                 if (h.k < 0) { finish_sample(L); continue; }
@@ -172,12 +184,6 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P, const
 // (:416-428) — because FP32 cannot hold t and barycentrics to 1e-5 on the millimetre-sized triangles of the
 // cornell-box table seen from 7 units away (|p| * 2^-24 / edge ~ 1e-4).  ~120 FP64 operations per ray against
 // ~2000 FP32 instructions of traversal.
-struct D3 { double x, y, z; };
-__device__ __forceinline__ D3 d3(double x, double y, double z) { D3 r; r.x = x; r.y = y; r.z = z; return r; }
-__device__ __forceinline__ D3 dsub(D3 a, D3 b) { return d3(a.x - b.x, a.y - b.y, a.z - b.z); }
-__device__ __forceinline__ double ddot(D3 a, D3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-__device__ __forceinline__ D3 dcross(D3 a, D3 b) { return d3(a.y * b.z - b.y * a.z, b.x * a.z - a.x * b.z, a.x * b.y - b.x * a.y); }
-
 __device__ __forceinline__ void refine_hit_fp64(const double* __restrict__ pos, const int face, const float3 of, const float3 df,
                                                 float& t_out, float& u_out, float& v_out) {
     const double* q = pos + 9 * (size_t)face;
@@ -205,32 +211,6 @@ __device__ __forceinline__ void refine_hit_fp64(const double* __restrict__ pos, 
 // intersect(Ray&, Face&, Vertex&) (MTPC/sceneManagement.cpp:316-338) with Face::norm from calNorm (:408-412), then
 // t = (p.x - o.x) / d.x > 0 and "smallest t wins, ties to the lowest leaf" of bvh_intersect (MTPC/pathTracing.cpp:347-361).
 // 1-3 candidates per ray reach the FP64 test; the traversal prunes against the FP32 image of the best t pushed out by 2e-4.
-__device__ __forceinline__ D3 dsub_rn(D3 a, D3 b) { return d3(__dsub_rn(a.x, b.x), __dsub_rn(a.y, b.y), __dsub_rn(a.z, b.z)); }
-__device__ __forceinline__ double ddot_rn(D3 a, D3 b) {   // Vertex::operator*(Vertex): (x*x2 + y*y2) + z*z2
-    return __dadd_rn(__dadd_rn(__dmul_rn(a.x, b.x), __dmul_rn(a.y, b.y)), __dmul_rn(a.z, b.z));
-}
-__device__ __forceinline__ D3 dcross_rn(D3 a, D3 b) {     // Vertex::cross, MTPC/sceneManagement.h:69-75
-    return d3(__dsub_rn(__dmul_rn(a.y, b.z), __dmul_rn(b.y, a.z)), __dsub_rn(__dmul_rn(b.x, a.z), __dmul_rn(a.x, b.z)),
-              __dsub_rn(__dmul_rn(a.x, b.y), __dmul_rn(b.x, a.y)));
-}
-// The reference's verdict on (ray, face): true iff the face is hit with t > 0; t_out = its t.
-__device__ __noinline__ bool reference_tri_test_fp64(const double* __restrict__ pos, const int face, const D3 o, const D3 d, double& t_out) {
-    const double* q = pos + 9 * (size_t)face;
-    const D3 v1 = d3(q[0], q[1], q[2]), v2 = d3(q[3], q[4], q[5]), v3 = d3(q[6], q[7], q[8]);
-    D3 n = dcross_rn(dsub_rn(v1, v2), dsub_rn(v3, v1));                       // Face::calNorm
-    const double nl = __dsqrt_rn(ddot_rn(n, n));
-    n = d3(__ddiv_rn(n.x, nl), __ddiv_rn(n.y, nl), __ddiv_rn(n.z, nl));
-    const double t = __ddiv_rn(ddot_rn(dsub_rn(v1, o), n), ddot_rn(n, d));
-    const D3 p = d3(__dadd_rn(o.x, __dmul_rn(d.x, t)), __dadd_rn(o.y, __dmul_rn(d.y, t)), __dadd_rn(o.z, __dmul_rn(d.z, t)));
-    const D3 ap = dsub_rn(p, v1), bp = dsub_rn(p, v2), cp = dsub_rn(p, v3);
-    const D3 ab = dsub_rn(v2, v1), bc = dsub_rn(v3, v2), ca = dsub_rn(v1, v3);
-    const double dir1 = ddot_rn(dcross_rn(ab, ap), n), dir2 = ddot_rn(dcross_rn(bc, bp), n), dir3 = ddot_rn(dcross_rn(ca, cp), n);
-    const double j1 = __dmul_rn(dir1, dir2), j2 = __dmul_rn(dir1, dir3), j3 = __dmul_rn(dir2, dir3);
-    if (!(j1 >= 0.0 && j2 >= 0.0 && j3 >= 0.0)) return false;                 // NaN (parallel ray) -> miss, as in the reference
-    t_out = __ddiv_rn(__dsub_rn(p.x, o.x), d.x);                              // MTPC/pathTracing.cpp:347
-    return t_out > 0.0;
-}
-
 template <bool COUNT>
 __device__ __forceinline__ void exact_leaf(const DeviceScene& sc, const int ref, const RayCtx& r, const D3 o64, const D3 d64, Hit& best,
                                            double& best64, unsigned& n_tris) {
@@ -271,7 +251,7 @@ __device__ __forceinline__ Hit trace_closest_exact(const DeviceScene& sc, const 
     int node = sc.root;
     while (node != MCPT_SENT) {
 #if MCPT_WIDE
-        if (node >= 0) node4_step<COUNT>(sc.qnodes4, node, r, best.t, stack, sp, n_nodes);
+        if (node >= 0) node4_step<COUNT>(sc.qnodes4, node, r, best.t, LocalStack{stack}, sp, n_nodes);
 #else
         if (node >= 0) node_step<COUNT>(sc.qnodes, node, r, best.t, stack, sp, n_nodes);
 #endif
@@ -340,11 +320,10 @@ int launch_megakernel(const RenderParams& P, int flags, cudaStream_t stream) {
     const long long blocks = (warps * 32 + tpb - 1) / tpb;
     if (blocks <= 0 || blocks > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
     const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
-    const bool eo = !(flags & MCPT_FLAG_NO_SHADOW_EARLY_OUT);
-    if (count && reuse) pt_megakernel<true, true><<<(unsigned)blocks, tpb, 0, stream>>>(P, eo);
-    else if (count) pt_megakernel<true, false><<<(unsigned)blocks, tpb, 0, stream>>>(P, eo);
-    else if (reuse) pt_megakernel<false, true><<<(unsigned)blocks, tpb, 0, stream>>>(P, eo);
-    else pt_megakernel<false, false><<<(unsigned)blocks, tpb, 0, stream>>>(P, eo);
+    if (count && reuse) pt_megakernel<true, true><<<(unsigned)blocks, tpb, 0, stream>>>(P);
+    else if (count) pt_megakernel<true, false><<<(unsigned)blocks, tpb, 0, stream>>>(P);
+    else if (reuse) pt_megakernel<false, true><<<(unsigned)blocks, tpb, 0, stream>>>(P);
+    else pt_megakernel<false, false><<<(unsigned)blocks, tpb, 0, stream>>>(P);
     return (int)cudaGetLastError();
 }
 

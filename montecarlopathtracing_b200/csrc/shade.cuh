@@ -6,6 +6,7 @@
 // pick without pdf division (Q9).
 #pragma once
 #include "device_types.cuh"
+#include "exact.cuh"
 #include "philox.cuh"
 #include "trace.cuh"
 #include "vecmath.cuh"
@@ -19,10 +20,11 @@ __device__ __forceinline__ float3 add_rn(float3 a, float3 b) { return f3(__fadd_
 
 #define MCPT_PI 3.1415926f       /* MTPC/pathTracing.h:11 */
 #define MCPT_P_RR 0.6f           /* MTPC/pathTracing.cpp:237 */
+#define MCPT_SELF_EPS 1.0e-4f    /* 1 % of the reference's 0.01 ray offset */
 #define MCPT_MAX_DEPTH 64        /* reference recursion is unbounded; 0.6^64 ~ 6e-15 (same cap as the oracle) */
 enum { LOBE_DIFFUSE = 0, LOBE_SPECULAR = 1, LOBE_TRANSMISSION = 2 };
 
-struct PathVertex { float3 p, pn, kd, wo; int mat; };
+struct PathVertex { float3 p, pn, kd, wo; int mat; int k; float t; };   // k = sorted-leaf index of the vertex's triangle, t = length of the ray that found it
 
 // Hit -> shading point: position and barycentric normal (MTPC/pathTracing.cpp:345-351, not normalised),
 // material, kd or texel (MTPC/pathTracing.cpp:148-163).
@@ -36,6 +38,7 @@ __device__ __forceinline__ void make_vertex(const DeviceScene& sc, const Hit& h,
     vx.pn = f3(sa.x, sa.y, sa.z) * w + f3(sa.w, sb.x, sb.y) * h.u + f3(sb.z, sb.w, sc4.x) * h.v;
     vx.wo = -ray_d;
     vx.mat = __float_as_int(v0.w);
+    vx.k = h.k; vx.t = h.t;
     const DMaterial* m = &sc.materials[vx.mat];
     if (m->tex_id >= 0) {
         const DTexture tx = sc.textures[m->tex_id];
@@ -50,11 +53,24 @@ __device__ __forceinline__ void make_vertex(const DeviceScene& sc, const Hit& h,
     }
 }
 
+// MCPT_FLAG_JITTER: the primary ray of sample s of pixel (x, y) goes through (x + u, y + v) of the pixel grid, (u, v) two Philox
+// uniforms of their own stream; formed in FP64 like raygen_kernel's corner rays (generateImg, MTPC/pathTracing.cpp:276-308).
+__device__ __forceinline__ float3 jittered_primary_dir(const DCamera& cam, const int x, const int y, const unsigned seed_lo,
+                                                       const unsigned seed_hi, const unsigned pixel, const unsigned sample) {
+    const float4 u = philox_uniform4(0u, STREAM_JITTER, seed_lo, seed_hi, pixel, sample);
+    const double fx = (double)x + (double)u.x, fy = (double)y + (double)u.y;
+    const double dx = cam.start[0] - cam.pdy[0] * fy + cam.pdx[0] * fx - cam.eye[0];
+    const double dy = cam.start[1] - cam.pdy[1] * fy + cam.pdx[1] * fx - cam.eye[1];
+    const double dz = cam.start[2] - cam.pdy[2] * fy + cam.pdx[2] * fx - cam.eye[2];
+    const double l = sqrt(dx * dx + dy * dy + dz * dz);
+    return f3((float)(dx / l), (float)(dy / l), (float)(dz / l));
+}
+
 // One light's next-event estimate (MTPC/pathTracing.cpp:171-231).  Returns false when nothing can be
 // added (no triangle selected, receiver faces away, zero weight) so the shadow ray is not traced.
 // contrib = kd/pi * Le * |w.vn|/|vn| * |w.pn|/|pn| * A / max(1,d)^2 * (w.pn); the caller multiplies by V.
 __device__ __forceinline__ bool sample_light(const DeviceScene& sc, const DLight& L, const PathVertex& vx, const float4 u,
-                                             float3& ray_o, float3& ray_d, float& ray_tmax, float3& contrib) {
+                                             float3& ray_o, float3& ray_d, float& ray_tmax, float3& contrib, const bool anyhit = false) {
     const float rnd = u.x * sc.area0;  // quirk Q6
     const float* cdf = sc.light_cdf + L.first;
     int lo = 0, hi = L.n_search;      // first j with rnd < cdf[j]
@@ -79,7 +95,8 @@ __device__ __forceinline__ bool sample_light(const DeviceScene& sc, const DLight
     if (!(contrib.x != 0.0f || contrib.y != 0.0f || contrib.z != 0.0f)) return false;
     ray_o = vx.p + w * 0.01f;
     ray_d = w;
-    ray_tmax = (dist - 0.01f) * 1.0002f;  // the sampled triangle itself bounds the closest hit
+    // closest-hit rule: the sampled triangle itself bounds the closest hit; any-hit rule: stop short of the sampled point
+    ray_tmax = (dist - 0.01f) * (anyhit ? 0.9999f : 1.0002f);
     return true;
 }
 
@@ -123,11 +140,14 @@ __device__ __forceinline__ void next_ray(const DeviceScene& sc, const PathVertex
         const float fresnel = rf0 + (1.0f - rf0) * (a * a * a * a * a);
         const float4 uf = philox_uniform4(bounce, STREAM_FRESNEL, seed_lo, seed_hi, pixel, sample);
         if (fresnel < uf.x) {
-            ray_o = vx.p;  // no origin offset on this branch (:102,:109)
             weight = f3(1.0f, 1.0f, 1.0f);
-            if (refract_dir(inc, normal, n1 / n2, ray_d)) { lobe = LOBE_TRANSMISSION; return; }
-            ray_d = inc - normal * (2.0f * dot(inc, normal));
-            lobe = LOBE_SPECULAR; weight = ks;
+            if (refract_dir(inc, normal, n1 / n2, ray_d)) lobe = LOBE_TRANSMISSION;
+            else { ray_d = inc - normal * (2.0f * dot(inc, normal)); lobe = LOBE_SPECULAR; weight = ks; }
+            // no origin offset on this branch (:102,:109): whether the reference's ray hits its own triangle again is a property
+            // of its FP64 arithmetic (exact.cuh).  Reproduce the verdict, then start a hair behind the surface (the triangle is
+            // hit again, at the same point) or a hair in front of it (it is not), which FP32 traversal resolves reliably.
+            const bool again = reference_self_hit_fp64(sc.pos, sc.leaf_face[vx.k], vx.p, inc, vx.t, ray_d);
+            ray_o = vx.p + ray_d * (again ? -MCPT_SELF_EPS : MCPT_SELF_EPS);
             return;
         }
     }

@@ -113,13 +113,38 @@ __device__ __forceinline__ void pair_cswap(unsigned& ka, int& ra, unsigned& kb, 
     const unsigned k = p ? kb : ka; kb = p ? ka : kb; ka = k;
     const int r = p ? rb : ra; rb = p ? ra : rb; ra = r;
 }
-template <bool COUNT>
+// Where a traversal stack lives.  LocalStack: the thread's local-memory array (lanes at different depths touch different 128-B
+// lines: one L1 wavefront per distinct depth in the warp).  SmemStack (wf_trace with -DMCPT_SMEM_STACK=1): entry i of thread t
+// at word i * blockDim + t of the CTA's dynamic shared memory — bank = lane whatever the depth, one wavefront per access.
+struct LocalStack {
+    int* a;
+    __device__ __forceinline__ int get(const int i) const { return a[i]; }
+    __device__ __forceinline__ void put(const int i, const int v) const { a[i] = v; }
+};
+struct SmemStack {
+    int* base; int stride;   // base = &smem[threadIdx.x], stride = blockDim.x
+    __device__ __forceinline__ int get(const int i) const { return base[i * stride]; }
+    __device__ __forceinline__ void put(const int i, const int v) const { base[i * stride] = v; }
+};
+// The top MCPT_SMEM_TOP wide nodes (breadth-first layout: the top levels are the first nodes) staged in shared memory, 16-B
+// chunks rotated by the node index so that lanes reading chunk c of different nodes spread over the bank groups.
+#ifndef MCPT_SMEM_TOP
+#define MCPT_SMEM_TOP 0
+#endif
+#ifndef MCPT_SMEM_STACK
+#define MCPT_SMEM_STACK 0
+#endif
+__device__ __forceinline__ int top_slot(const int node, const int c) { return node * 4 + ((c + (node >> 1)) & 3); }
+
+template <bool COUNT, class Stack>
 __device__ __forceinline__ void node4_step(const QNode4* __restrict__ nodes, int& node, const RayCtx& r, const float best_t,
-                                           int* stack, int& sp, unsigned& n_nodes) {
-    const uint4 k0 = __ldg(&nodes[node].c[0]);
-    const uint4 k1 = __ldg(&nodes[node].c[1]);
-    const uint4 k2 = __ldg(&nodes[node].c[2]);
-    const uint4 k3 = __ldg(&nodes[node].c[3]);
+                                           const Stack stack, int& sp, unsigned& n_nodes, const uint4* __restrict__ top = nullptr) {
+    uint4 k0, k1, k2, k3;
+    if (MCPT_SMEM_TOP && top && node < MCPT_SMEM_TOP) {
+        k0 = top[top_slot(node, 0)]; k1 = top[top_slot(node, 1)]; k2 = top[top_slot(node, 2)]; k3 = top[top_slot(node, 3)];
+    } else {
+        k0 = __ldg(&nodes[node].c[0]); k1 = __ldg(&nodes[node].c[1]); k2 = __ldg(&nodes[node].c[2]); k3 = __ldg(&nodes[node].c[3]);
+    }
     if (COUNT) n_nodes++;
     const unsigned fx = r.sx ^ 0x0022u, fy = r.sy ^ 0x0022u, fz = r.sz ^ 0x0022u;
     unsigned s0 = slab_key(k0, r, fx, fy, fz, best_t), s1 = slab_key(k1, r, fx, fy, fz, best_t);
@@ -128,11 +153,11 @@ __device__ __forceinline__ void node4_step(const QNode4* __restrict__ nodes, int
     pair_cswap(s0, r0, s1, r1); pair_cswap(s2, r2, s3, r3); pair_cswap(s0, r0, s2, r2); pair_cswap(s1, r1, s3, r3); pair_cswap(s1, r1, s2, r2);
     // no bounds test: mcpt_build_bvh rejects (or rebuilds) a wide tree with more than MCPT_MAX_WIDE_LEVELS = 21 internal levels, and
     // a depth-first walk holds at most the sentinel + 3 siblings per level above the current node: sp <= 1 + 3*20 before the pushes
-    if (s3 != 0xFFFFFFFFu) { stack[sp] = r3; sp++; }
-    if (s2 != 0xFFFFFFFFu) { stack[sp] = r2; sp++; }
-    if (s1 != 0xFFFFFFFFu) { stack[sp] = r1; sp++; }
+    if (s3 != 0xFFFFFFFFu) { stack.put(sp, r3); sp++; }
+    if (s2 != 0xFFFFFFFFu) { stack.put(sp, r2); sp++; }
+    if (s1 != 0xFFFFFFFFu) { stack.put(sp, r1); sp++; }
     node = r0;
-    if (s0 == 0xFFFFFFFFu) node = stack[--sp];
+    if (s0 == 0xFFFFFFFFu) node = stack.get(--sp);
 }
 
 // Shadow rays (MTPC/pathTracing.cpp:202-215) ask one question: does the CLOSEST hit carry the light's material?  The answer is
@@ -224,7 +249,7 @@ __device__ __forceinline__ Hit trace_closest(const DeviceScene& sc, const float3
     int node = sc.root;
     while (node != MCPT_SENT) {
 #if MCPT_WIDE
-        if (node >= 0) node4_step<COUNT>(sc.qnodes4, node, r, best.t, stack, sp, n_nodes);
+        if (node >= 0) node4_step<COUNT>(sc.qnodes4, node, r, best.t, LocalStack{stack}, sp, n_nodes);
 #else
         if (node >= 0) node_step<COUNT>(sc.qnodes, node, r, best.t, stack, sp, n_nodes);
 #endif

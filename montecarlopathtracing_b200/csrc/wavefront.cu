@@ -94,11 +94,13 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
     __shared__ PushScratch push_sh;
     const int lane = threadIdx.x & 31;
     const int warp_id = slot >> 5;
-    const int group = warp_id / n_tiles, tile = warp_id % n_tiles;
-    const int x = (tile % tiles_x) * 8 + (lane & 7), y = (tile / tiles_x) * 4 + (lane >> 3);
+    const int group = (int)fastdiv((unsigned)warp_id, P.div_tiles), tile = warp_id - group * n_tiles;
+    const int tile_y = (int)fastdiv((unsigned)tile, P.div_tiles_x);
+    const int x = (tile - tile_y * tiles_x) * 8 + (lane & 7), y = tile_y * 4 + (lane >> 3);
     const bool valid = slot < B.slot_end && x < W && y < H;
     const unsigned pixel = (unsigned)(y * W + x);
     const int nl = sc.n_lights;
+    const bool jitter = (P.flags & MCPT_FLAG_JITTER) != 0, anyhit = (P.flags & MCPT_FLAG_ANYHIT_SHADOW) != 0;
 
     int state = WF_DONE, lobe = LOBE_DIFFUSE, chunk = 0, s = 0;
     bool has_extend = false, have_hit0 = false, have_vertex = false, emit_primary = false, store_hit0 = false;
@@ -154,7 +156,8 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
             const int m = __float_as_int(__ldg(&sc.tri[h.k].v0m).w);
             const int li = sc.materials[m].light_id;
             if (li >= 0) { finish_sample(f3(sc.lights[li].radiance[0], sc.lights[li].radiance[1], sc.lights[li].radiance[2])); return; }
-            hv = h; vdir = cam_d; have_vertex = true;
+            hv = h; have_vertex = true;
+            vdir = jitter ? jittered_primary_dir(P.cam, x, y, P.seed_lo, P.seed_hi, pixel, (unsigned)s) : cam_d;
             beta = f3(1.f, 1.f, 1.f); L = f3(0.f, 0.f, 0.f); bounce = 0;
         };
         if (state == WF_NEW) {
@@ -209,14 +212,14 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
     }
 
     // ---- emission: the whole warp walks the lights together so every push is one ballot + one atomic ----
-    PathVertex vx; vx.mat = 0; vx.p = vx.pn = vx.kd = vx.wo = f3(0.f, 0.f, 0.f);
+    PathVertex vx; vx.mat = 0; vx.k = 0; vx.t = 0.f; vx.p = vx.pn = vx.kd = vx.wo = f3(0.f, 0.f, 0.f);
     if (have_vertex) { make_vertex(sc, hv, vdir, vx); __stcg(&B.vis[slot], 0u); }
     for (int l = 0; l < nl; l++) {
         bool ok = false;
         float3 o = f3(0.f, 0.f, 0.f), d = o, contrib = o; float tmax = 0.f;
         if (have_vertex) {
             const float4 u = philox_uniform4(bounce, STREAM_LIGHT0 + l, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
-            ok = sample_light(sc, sc.lights[l], vx, u, o, d, tmax, contrib);
+            ok = sample_light(sc, sc.lights[l], vx, u, o, d, tmax, contrib, anyhit);
             if (ok) { const float3 bp = mul_rn(beta, contrib); __stcg(&B.pend[(size_t)l * B.n_slots + slot], make_float4(bp.x, bp.y, bp.z, 0.f)); }
         }
         push_ray(ok, B, tail, o, d, tmax, (unsigned)slot | ((unsigned)(l + 1) << WF_ID_BITS), push_sh, l);
@@ -224,6 +227,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
     {
         bool ext = false;
         float3 o = cam_o, d = cam_d;
+        if (emit_primary && jitter) d = jittered_primary_dir(P.cam, x, y, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
         if (have_vertex) {
             const float4 u = philox_uniform4(bounce, STREAM_PATH, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
             if (u.x < MCPT_P_RR && bounce + 1 < MCPT_MAX_DEPTH) {   // russian_Roulette (:3-11,:240)
@@ -278,7 +282,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
 template <bool COUNT>
 __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const DeviceScene sc, const WfBuffers B, const int iter, unsigned long long* stats,
                                                 const int refill_min, const int leaf_min, const int block_min,
-                                                const int node_steps, const bool early_out) {
+                                                const int node_steps, const int flags) {
     const int par = iter & 1;
     const unsigned n = __ldcg(B.counters + WFC_TAIL + par);
     unsigned* head = B.counters + WFC_HEAD + par;
@@ -290,8 +294,25 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&stats[0], (unsigned long long)n);
     RayCtx r = ray_setup(f3(0.f, 0.f, 0.f), f3(1.f, 1.f, 1.f), sc.qgrid);
     Hit best; best.t = 0.f; best.u = 0.f; best.v = 0.f; best.k = -1;
-    int stack[MCPT_STACK_SIZE + 4];
-    stack[0] = MCPT_SENT;
+    extern __shared__ __align__(16) unsigned char wf_smem[];
+#if MCPT_SMEM_TOP
+    // north_star (b): the top tree levels staged in shared memory — here the first MCPT_SMEM_TOP wide nodes, copied once per CTA
+    uint4* top = reinterpret_cast<uint4*>(wf_smem);
+    for (int i = threadIdx.x; i < MCPT_SMEM_TOP * 4; i += blockDim.x) {
+        const int nd = i >> 2, c = i & 3;
+        top[top_slot(nd, c)] = nd < sc.n_wide ? __ldg(&sc.qnodes4[nd].c[c]) : make_uint4(0x0000FFFFu, 0x0000FFFFu, 0x0000FFFFu, 0x80000000u);
+    }
+    __syncthreads();
+#else
+    const uint4* top = nullptr;
+#endif
+#if MCPT_SMEM_STACK
+    const SmemStack stack{reinterpret_cast<int*>(wf_smem + MCPT_SMEM_TOP * 64) + threadIdx.x, (int)blockDim.x};
+#else
+    int stack_mem[MCPT_STACK_SIZE + 4];
+    const LocalStack stack{stack_mem};
+#endif
+    stack.put(0, MCPT_SENT);
     int sp = 1, node = MCPT_SENT;
     unsigned id = 0;
     Occluder oc = no_occluder();
@@ -300,6 +321,8 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
         const unsigned slot = id & ((1u << WF_ID_BITS) - 1u), kind = id >> WF_ID_BITS;
         if (kind == 0u) {
             __stcg(&B.hit[slot], make_float4(best.t, best.u, best.v, __int_as_float(best.k)));
+        } else if (flags & MCPT_FLAG_ANYHIT_SHADOW) {
+            if (best.k < 0) atomicOr(&B.vis[slot], 1u << (kind - 1));   // quality extension: visible iff nothing is in between
         } else if (best.k >= 0 && __float_as_int(__ldg(&sc.tri[best.k].v0m).w) == sc.lights[kind - 1].mat_id) {
             atomicOr(&B.vis[slot], 1u << (kind - 1));   // visible iff the CLOSEST hit carries the light's material (:212-215)
         }
@@ -329,7 +352,11 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
                         best.t = o4.w; best.u = 0.f; best.v = 0.f; best.k = -1;
                         sp = 1; has_ray = true;
                         const unsigned kind = id >> WF_ID_BITS;
-                        oc = (early_out && kind != 0u) ? shadow_occluder(sc.lights[kind - 1], f3(o4), f3(d4), o4.w) : no_occluder();
+                        oc = no_occluder();
+                        if (kind != 0u) {
+                            if (flags & MCPT_FLAG_ANYHIT_SHADOW) { oc.t = 3.0e38f; oc.light_mat = -2; }   // any hit settles it
+                            else if (!(flags & MCPT_FLAG_NO_SHADOW_EARLY_OUT)) oc = shadow_occluder(sc.lights[kind - 1], f3(o4), f3(d4), o4.w);
+                        }
                         node = (d4.x == 0.0f) ? MCPT_SENT : sc.root;   // quirk Q2: d.x == 0 hits nothing
                     }
                 }
@@ -346,14 +373,14 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
                 if (at_node != 0u && lane == 0) { w_node++; w_idle += __popc(idle_m); w_fin += __popc(fin_m); }
             }
 #if MCPT_WIDE
-            if (node >= 0) node4_step<COUNT>(sc.qnodes4, node, r, best.t, stack, sp, n_nodes);
+            if (node >= 0) node4_step<COUNT>(sc.qnodes4, node, r, best.t, stack, sp, n_nodes, top);
 #else
-            if (node >= 0) node_step<COUNT>(sc.qnodes, node, r, best.t, stack, sp, n_nodes);
+            if (node >= 0) node_step<COUNT>(sc.qnodes, node, r, best.t, stack_mem, sp, n_nodes);
 #endif
             if (node < 0 && node != MCPT_SENT) {
-                if (pend == 0) { pend = node; node = stack[--sp]; }
+                if (pend == 0) { pend = node; node = stack.get(--sp); }
 #if MCPT_PEND2
-                else if (pend2 == 0) { pend2 = node; node = stack[--sp]; }
+                else if (pend2 == 0) { pend2 = node; node = stack.get(--sp); }
 #endif
             }
         }
@@ -466,10 +493,17 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
     for (int k = 1; k < pipes; k++) WF_CU(cudaStreamWaitEvent(pp[k].st, ev_fork, 0));
 
     const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
-    const bool early_out = !(flags & MCPT_FLAG_NO_SHADOW_EARLY_OUT);
     const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 12) / pipes;   // CTAs of 4 warps, shared by the pipes
     const int refill_min = env_int("MCPT_REFILL_MIN", 12), leaf_min = env_int("MCPT_LEAF_MIN", 1),
               block_min = env_int("MCPT_BLOCK_MIN", 1), node_steps = env_int("MCPT_NODE_STEPS", MCPT_WIDE ? 2 : 4);
+    // A/B builds only (-DMCPT_SMEM_STACK=1 / -DMCPT_SMEM_TOP=K): dynamic shared memory of wf_trace = staged top nodes + a stack of
+    // 1 + 3 * (levels of this scene's wide tree) entries per thread, thread-interleaved
+    size_t trace_smem = 0;
+#if MCPT_SMEM_TOP || MCPT_SMEM_STACK
+    trace_smem = (size_t)MCPT_SMEM_TOP * 64 + (MCPT_SMEM_STACK ? (size_t)(4 + 3 * P.scene.wide_levels) * 128 * 4 : 0);
+    WF_CU(cudaFuncSetAttribute(wf_trace<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)trace_smem));
+    WF_CU(cudaFuncSetAttribute(wf_trace<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)trace_smem));
+#endif
     const int batch = 8;
     const bool diag = getenv("MCPT_DIAG_ALIVE") != nullptr;
     int nlaunch = 0, n_timed = 0;
@@ -487,8 +521,8 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
                     H.trace_events.push_back(ev);
                 }
                 cudaEventRecord(H.trace_events[2 * n_timed], q.st);
-                if (count) wf_trace<true><<<trace_blocks, 128, 0, q.st>>>(P.scene, q.B, iter, P.counters, refill_min, leaf_min, block_min, node_steps, early_out);
-                else wf_trace<false><<<trace_blocks, 128, 0, q.st>>>(P.scene, q.B, iter, P.counters, refill_min, leaf_min, block_min, node_steps, early_out);
+                if (count) wf_trace<true><<<trace_blocks, 128, trace_smem, q.st>>>(P.scene, q.B, iter, P.counters, refill_min, leaf_min, block_min, node_steps, flags);
+                else wf_trace<false><<<trace_blocks, 128, trace_smem, q.st>>>(P.scene, q.B, iter, P.counters, refill_min, leaf_min, block_min, node_steps, flags);
                 cudaEventRecord(H.trace_events[2 * n_timed + 1], q.st);
                 n_timed++; nlaunch += 2;
             }

@@ -300,8 +300,8 @@ static void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, ui
 MCPT_API void orc_philox(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
     philox4x32_10(ctr[0], ctr[1], ctr[2], ctr[3], key[0], key[1], out);
 }
-typedef struct { uint32_t pixel, sample, seed_lo, seed_hi; long n_shadow, n_extend; } Rng;
-enum { STREAM_PATH = 0, STREAM_FRESNEL = 1, STREAM_LIGHT0 = 2 };
+typedef struct { uint32_t pixel, sample, seed_lo, seed_hi; long n_shadow, n_extend; int flags; } Rng;
+enum { STREAM_PATH = 0, STREAM_FRESNEL = 1, STREAM_LIGHT0 = 2, STREAM_JITTER = 0x7FFFFFFF };
 static void draw4(const Rng* g, int bounce, int stream, double u[4]) {
     uint32_t o[4];
     philox4x32_10((uint32_t)bounce, (uint32_t)stream, g->seed_lo, g->seed_hi, g->pixel, g->sample, o);
@@ -405,6 +405,10 @@ static V3 shade(const orc_scene* S, const Isect* p, V3 wo, Rng* g, int bounce) {
         Isect inter;
         double visibility = 1;
         g->n_shadow++;
+        if (g->flags & MCPT_FLAG_ANYHIT_SHADOW) {   /* quality extension (twin of the CUDA flag): visible iff nothing lies in between */
+            double tmax = (vnorm(vsub(xl, p->p)) - 0.01) * 0.9999;
+            if (ray_intersect(S, &rl, &inter) && inter.t < tmax) visibility = 0;
+        } else
         if (!ray_intersect(S, &rl, &inter) || S->tri[inter.k].mat != sf->mat) visibility = 0; /* :212-215 closest hit, by material */
         if (vdot(direction, p->pn) > 0) {
             double pdf_light = (double)1 / total_area;
@@ -443,8 +447,15 @@ static V3 shade(const orc_scene* S, const Isect* p, V3 wo, Rng* g, int bounce) {
 
 /* generateImg, MTPC/pathTracing.cpp:274-331.  Samples [s0,s1) of spp are integrated; img gets their SUM / spp.
  * counts3 = {primary, shadow, extend} closest-hit queries. */
+MCPT_API void orc_render_flags(const orc_scene* S, const mcpt_camera* cam, int width, int height, int spp, int s0, int s1,
+                               uint64_t seed, int flags, double* img, double* counts3);
 MCPT_API void orc_render(const orc_scene* S, const mcpt_camera* cam, int width, int height, int spp, int s0, int s1,
                          uint64_t seed, double* img, double* counts3) {
+    orc_render_flags(S, cam, width, height, spp, s0, s1, seed, 0, img, counts3);
+}
+/* flags: MCPT_FLAG_JITTER / MCPT_FLAG_ANYHIT_SHADOW, the CPU twins of the CUDA integrator's quality extensions (include/mcpt.h). */
+MCPT_API void orc_render_flags(const orc_scene* S, const mcpt_camera* cam, int width, int height, int spp, int s0, int s1,
+                               uint64_t seed, int flags, double* img, double* counts3) {
     V3 up = vnormalize(v3(cam->up[0], cam->up[1], cam->up[2]));
     V3 eye = v3(cam->eye[0], cam->eye[1], cam->eye[2]), look = v3(cam->lookat[0], cam->lookat[1], cam->lookat[2]);
     if (width <= 0) width = cam->width;
@@ -465,10 +476,16 @@ MCPT_API void orc_render(const orc_scene* S, const mcpt_camera* cam, int width, 
             double acc[3] = {0, 0, 0};
             for (int k = s0; k < s1; k++) {
                 Ray ray; ray.o = eye; ray.d = vnormalize(vsub(pos, eye));   /* quirk Q4: same ray for every sample */
+                Rng g = {(uint32_t)(i * width + j), (uint32_t)k, (uint32_t)seed, (uint32_t)(seed >> 32), 0, 0, flags};
+                if (flags & MCPT_FLAG_JITTER) {   /* through (j + u, i + v) of the pixel grid instead of its corner */
+                    double u[4];
+                    draw4(&g, 0, STREAM_JITTER, u);
+                    V3 pj = vadd(vsub(start, vmul(screen_pdy, (double)i + u[1])), vmul(screen_pdx, (double)j + u[0]));
+                    ray.d = vnormalize(vsub(pj, eye));
+                }
                 Isect ret;
                 np++;
                 if (ray_intersect(S, &ray, &ret)) {
-                    Rng g = {(uint32_t)(i * width + j), (uint32_t)k, (uint32_t)seed, (uint32_t)(seed >> 32), 0, 0};
                     V3 rad = shade(S, &ret, vneg(ray.d), &g, 0);
                     acc[0] += rad.x / spp; acc[1] += rad.y / spp; acc[2] += rad.z / spp;
                     ns += g.n_shadow; ne += g.n_extend;

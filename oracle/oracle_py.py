@@ -41,6 +41,8 @@ def lib():
         _lib.orc_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib.orc_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64,
                                     C.c_void_p, C.c_void_p]
+        _lib.orc_render_flags.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int,
+                                          C.c_void_p, C.c_void_p]
         _lib.orc_philox.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     return _lib
 
@@ -99,12 +101,13 @@ class OracleScene:
         return {"hit": hit, "face": face, "leaf": leaf, "t": rec[:, 0], "p": rec[:, 1:4], "pn": rec[:, 4:7],
                 "box_tests": cnt[0], "tri_tests": cnt[1]}
 
-    def render(self, camera, spp, width=0, height=0, s0=0, s1=None, seed=0):
+    def render(self, camera, spp, width=0, height=0, s0=0, s1=None, seed=0, flags=0):
+        """flags: MCPT_FLAG_JITTER (8) / MCPT_FLAG_ANYHIT_SHADOW (16), the twins of the CUDA integrator's quality extensions."""
         w = width if width > 0 else camera.width
         h = height if height > 0 else camera.height
         img, cnt = np.zeros((h, w, 3), np.float64), np.zeros(3, np.float64)
-        lib().orc_render(self._s, C.addressof(camera), w, h, spp, s0, spp if s1 is None else s1, seed, img.ctypes.data,
-                         cnt.ctypes.data)
+        lib().orc_render_flags(self._s, C.addressof(camera), w, h, spp, s0, spp if s1 is None else s1, seed, flags, img.ctypes.data,
+                               cnt.ctypes.data)
         return img, {"primary": cnt[0], "shadow": cnt[1], "extend": cnt[2]}
 
 

@@ -1,0 +1,12 @@
+#!/bin/bash
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -q > gpurun_out/f_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/f_pytest.log
+tail -6 gpurun_out/f_pytest.log
+q() { python tools/profile_render.py --workload $1 --spp $2 --renders 3 --builds 5 | python -c "
+import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$3', d['workload'], d['spp'], 'render_ms', round(d['render_ms'],2), 'Msamples/s', round(d['samples']/3/d['render_ms']*1e-3,1), 'build_ms', round(d['build_ms'],3))"; }
+for lib in "" sstack stop sboth; do
+for spec in cornell-box-1024x1024:256 veach-mis-1200x900:100 synthetic-5M-1920x1080:64; do
+  w=${spec%%:*}; s=${spec##*:}
+  if [ -z "$lib" ]; then q $w $s base; else MCPT_LIB=$PWD/montecarlopathtracing_b200/libmcpt_$lib.so q $w $s $lib; fi
+done; done
+for ctas in 8 10; do MCPT_TRACE_CTAS_PER_SM=$ctas MCPT_LIB=$PWD/montecarlopathtracing_b200/libmcpt_sstack.so q cornell-box-1024x1024 256 sstack-ctas$ctas; done
