@@ -244,6 +244,7 @@ class Context:
     def comm_init(self, world, rank, comm_id):
         """Join this context to the render's NCCL communicator; comm_id = the 128 bytes rank 0 got from comm_unique_id()."""
         check(lib().mcpt_comm_init(self._c, int(world), int(rank), bytes(comm_id)))
+        self._rank = int(rank)
 
     def comm_destroy(self):
         check(lib().mcpt_comm_destroy(self._c))
@@ -255,6 +256,7 @@ class Context:
         h = height if height > 0 else camera.height
         st = capi.Stats()
         ptr = None
+        to_host = to_host and getattr(self, "_rank", 0) == 0
         if to_host:
             if out is None:
                 out = np.empty((h, w, 3), np.float32)

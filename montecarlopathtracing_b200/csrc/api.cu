@@ -634,6 +634,13 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
         if (want > (1LL << 25)) want = 1LL << 25;
     }
     while (g > 1 && (long long)width * height * (nch / g) < want) g >>= 1;
+    if (mode == MCPT_MODE_WAVEFRONT) {
+        // at least four slots per pixel where that fits (2^25 slots): wf_shade hands a pixel's chunks out dynamically, which only
+        // shortens the render's tail when a pixel has more than one slot to share them (3840 x 2160 and veach-mis had one)
+        const char* v = getenv("MCPT_WF_MIN_GROUPS");
+        int min_groups = v && *v ? atoi(v) : 4;   // measured 1 / 2 / 4: 3840x2160 3135 / 3277 / 3296 Msamples/s, veach-mis 712 / 729 / 733, 5 M triangles 946 / 945 / 967
+        while (g > 1 && nch / g < min_groups && (long long)width * height * (nch / (g >> 1)) <= (1LL << 25)) g >>= 1;
+    }
     P.chunks_per_thread = g;
     P.flags = flags;
     P.div_tiles_x = make_fastdiv((unsigned)((width + 7) >> 3));
@@ -646,7 +653,7 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
         const int n_slots = wavefront_slots(P);
         if (n_slots < 0) return fail_arg("render: image too large for one wavefront pass (more than 2^26 path slots)");
         if (c->n_lights > 32) return fail_arg("render: wavefront mode supports at most 32 lights");
-        CU(grow(c->d_wf, c->wf_cap, wavefront_scratch_bytes(n_slots, c->n_lights)));
+        CU(grow(c->d_wf, c->wf_cap, wavefront_scratch_bytes(n_slots, c->n_lights, (long long)width * height)));
         const int e = launch_wavefront(P, flags, c->d_wf, c->wfh, c->stream, launches);
         if (e) return fail_cuda((cudaError_t)e, "wavefront loop");
     } else {

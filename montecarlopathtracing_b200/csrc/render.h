@@ -14,7 +14,7 @@ int launch_megakernel(const RenderParams& P, int flags, cudaStream_t stream);
 // K8+K9: wavefront integrator (wavefront.cu); same planes as the megakernel, bit for bit.  The host reads the number of live path
 // slots one batch of iterations behind the GPU, so the stream never idles waiting for it.
 int wavefront_slots(const RenderParams& P);                    // < 0: too many slots for the 26-bit ray id
-size_t wavefront_scratch_bytes(int n_slots, int n_lights);
+size_t wavefront_scratch_bytes(int n_slots, int n_lights, long long n_pixels);
 enum { WF_MAX_PIPES = 4 };
 struct WfHost {   // per-context host resources of the wavefront loop (created on first use)
     std::vector<cudaStream_t> side_streams;

@@ -35,6 +35,21 @@ __device__ __forceinline__ float __frcp_approx(const float x) { float y; asm("rc
 // t = (2^23 + q)*a + (b - 2^23*a): one PRMT and one FMA per plane.  b' = b - 2^23*a is rounded to half a grid cell
 // at worst, which the two-cell outward push of the quantiser covers (lbvh.cu K4).
 struct RayCtx { float3 o, d; float ax, ay, az, bx, by, bz; unsigned sx, sy, sz; };
+// sm_100a issues packed pairs of FP32 FMAs as ONE instruction (FFMA2, PTX fma.rn.f32x2): the slab planes of a child pair up as
+// (near x, near y), (far x, far y), (near z, far z): three FFMA2 instead of six FFMA per child.  Measured and NOT kept
+// (-DMCPT_FFMA2=1 builds it): the operands must sit in aligned 64-bit register pairs, wf_trace starts spilling at its 56-register
+// budget, and throughput DROPS: cornell-box 1 805 -> 1 738 Msamples/s, veach-mis 736 -> 717, 5 M triangles 974 -> 915.
+#ifndef MCPT_FFMA2
+#define MCPT_FFMA2 0
+#endif
+__device__ __forceinline__ unsigned long long pack2(const float lo, const float hi) {
+    unsigned long long r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r;
+}
+__device__ __forceinline__ void fma2(const float a0, const float a1, const unsigned long long b, const unsigned long long c, float& r0, float& r1) {
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pack2(a0, a1)), "l"(b), "l"(c));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r0), "=f"(r1) : "l"(r));
+}
 
 __device__ __forceinline__ RayCtx ray_setup(const float3 o, const float3 d, const QGrid* __restrict__ grid) {
     RayCtx r; r.o = o; r.d = d;
@@ -101,9 +116,17 @@ __device__ __forceinline__ void node_step(const QNode* __restrict__ nodes, int& 
 // ran on nearly every step for 2-6 of 32 lanes, ~40 of the step's ~150 instructions).
 __device__ __forceinline__ unsigned slab_key(const uint4 k, const RayCtx& r, const unsigned fx, const unsigned fy, const unsigned fz,
                                              const float best_t) {
+#if MCPT_FFMA2
+    float nx, ny, gx, gy, nz, gz;
+    const unsigned long long axy = pack2(r.ax, r.ay), bxy = pack2(r.bx, r.by), azz = pack2(r.az, r.az), bzz = pack2(r.bz, r.bz);
+    fma2(q_sel(k.x, r.sx), q_sel(k.y, r.sy), axy, bxy, nx, ny);
+    fma2(q_sel(k.x, fx), q_sel(k.y, fy), axy, bxy, gx, gy);
+    fma2(q_sel(k.z, r.sz), q_sel(k.z, fz), azz, bzz, nz, gz);
+#else
     const float nx = fmaf(q_sel(k.x, r.sx), r.ax, r.bx), gx = fmaf(q_sel(k.x, fx), r.ax, r.bx);
     const float ny = fmaf(q_sel(k.y, r.sy), r.ay, r.by), gy = fmaf(q_sel(k.y, fy), r.ay, r.by);
     const float nz = fmaf(q_sel(k.z, r.sz), r.az, r.bz), gz = fmaf(q_sel(k.z, fz), r.az, r.bz);
+#endif
     const float cmin = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
     const float cmax = fminf(fminf(gx, gy), fminf(gz, best_t));
     return cmin <= cmax ? __float_as_uint(cmin) : 0xFFFFFFFFu;

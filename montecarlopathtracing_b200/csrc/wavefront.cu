@@ -39,6 +39,7 @@ struct WfBuffers {
     float4* pend;    // [light][slot]: throughput * unshadowed NEE contribution of the vertex in flight
     unsigned* vis;   // shadow-ray results, bit l = light l visible
     unsigned char* warp_done;  // [slot / 32]: every slot of that warp is DONE (or outside the image): wf_shade reads nothing else
+    int* next_chunk;           // [pixel]: how many of the launch's chunks the pixel's slots have taken so far (dynamic hand-out)
     float4* ray_o;   // queue: origin, tmax
     float4* ray_d;   // queue: direction, id = slot | (kind << 26), kind 0 = primary/extend, l+1 = shadow ray of light l
     unsigned* counters;
@@ -110,7 +111,12 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
     const float3 cam_o = f3((float)P.cam.eye[0], (float)P.cam.eye[1], (float)P.cam.eye[2]);
     Hit hit0; hit0.t = 0.f; hit0.u = 0.f; hit0.v = 0.f; hit0.k = -1;
     Hit hv = hit0;
-    const int chunk_first = P.chunk_begin + group * P.chunks_per_thread, chunk_end = chunk_first + P.chunks_per_thread;
+    // Chunks are handed out DYNAMICALLY to the slots of a pixel (one atomic counter per pixel): a chunk's plane is the same pure
+    // function of (seed, pixel, its samples) whichever slot integrates it — and every slot of a pixel has the same cached
+    // primary hit — so the image cannot change, but the slots of a pixel now finish within one chunk of each other.  With the
+    // static split a slot whose 64 samples happened to run long kept the render's tail going for ~80 nearly empty iterations.
+    const int chunk_end = P.chunk_begin + P.n_chunks;
+    (void)group;
     float4 ss_in = make_float4(0.f, 0.f, 0.f, 0.f), h0_in = ss_in, hit_in = ss_in, L_in = ss_in, rd_in = ss_in;
     unsigned vis_in = 0u;
     // Finished warps cost one byte: at 3840 x 2160 the 16:9 frame looks past the box on both sides, ~45 % of the slots are DONE
@@ -128,7 +134,8 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
     if (valid && !warp_was_done) {
         cam_d = f3(__ldg(P.cam_dirs + 3 * (size_t)pixel), __ldg(P.cam_dirs + 3 * (size_t)pixel + 1), __ldg(P.cam_dirs + 3 * (size_t)pixel + 2));
         if (iter == 0) {
-            state = WF_NEW; chunk = chunk_first; s = (int)((long long)chunk * P.spp / MCPT_NUM_CHUNKS);
+            state = WF_NEW; chunk = P.chunk_begin + atomicAdd(&B.next_chunk[pixel], 1);
+            s = (int)((long long)chunk * P.spp / MCPT_NUM_CHUNKS);
         } else {
             // all of the slot's state is requested at once (independent 16-B loads in flight) and decoded afterwards:
             // the kernel is latency-bound, not bandwidth-bound (ncu: 30 % issue, 21 % DRAM)
@@ -196,11 +203,12 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
         }
         while (need_sample) {
             need_sample = false;
-            while (s >= s_end && chunk < chunk_end) {   // chunk complete (or empty): write its plane
+            while (s >= s_end && chunk < chunk_end) {   // chunk complete (or empty): write its plane, take the pixel's next one
                 float* out = P.planes + (size_t)(chunk - P.chunk_begin) * ((size_t)W * H * 3) + (size_t)pixel * 3;
                 out[0] = sum.x; out[1] = sum.y; out[2] = sum.z;
                 sum = f3(0.f, 0.f, 0.f);
-                chunk++;
+                chunk = P.chunk_begin + atomicAdd(&B.next_chunk[pixel], 1);
+                s = (int)((long long)chunk * P.spp / MCPT_NUM_CHUNKS);
                 s_end = (int)((long long)(chunk + 1) * P.spp / MCPT_NUM_CHUNKS);
             }
             if (chunk >= chunk_end) { state = WF_DONE; break; }
@@ -425,9 +433,9 @@ int wavefront_slots(const RenderParams& P) {
     return n < (1LL << WF_ID_BITS) ? (int)n : -1;
 }
 
-size_t wavefront_scratch_bytes(int n_slots, int n_lights) {
+size_t wavefront_scratch_bytes(int n_slots, int n_lights, long long n_pixels) {
     const size_t n = (size_t)n_slots;
-    return 6 * align256(16 * n) + align256(16 * n * (size_t)(n_lights > 0 ? n_lights : 1)) + align256(4 * n) + align256(n / 32 + 1) +
+    return 6 * align256(16 * n) + align256(16 * n * (size_t)(n_lights > 0 ? n_lights : 1)) + align256(4 * n) + align256(n / 32 + 1) + align256(4 * (size_t)n_pixels) +
            2 * align256(16 * n * (size_t)(n_lights + 1)) + align256(4 * WFC_COUNT * WF_MAX_PIPES);
 }
 
@@ -467,6 +475,9 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
     B0.pend = (float4*)take(16 * n * (size_t)(nl > 0 ? nl : 1));
     B0.vis = (unsigned*)take(4 * n);
     B0.warp_done = (unsigned char*)take(n / 32 + 1);
+    const size_t n_pixels = (size_t)P.cam.width * P.cam.height;
+    B0.next_chunk = (int*)take(4 * n_pixels);
+    WF_CU(cudaMemsetAsync(B0.next_chunk, 0, 4 * n_pixels, stream));
     B0.ray_o = (float4*)take(16 * n * (size_t)(nl + 1)); B0.ray_d = (float4*)take(16 * n * (size_t)(nl + 1));
     B0.counters = (unsigned*)take(4 * WFC_COUNT * WF_MAX_PIPES);
     B0.n_slots = n_slots;

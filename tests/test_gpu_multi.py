@@ -47,7 +47,8 @@ def test_one_process_all_gpus_is_bit_identical(scenes, single, tmp_path):
             for mode in (M.MODE_WAVEFRONT, M.MODE_MEGAKERNEL):
                 img = m.render(s.camera, spp, w, h, mode=mode)
                 assert np.array_equal(img.view(np.uint32), base.view(np.uint32)), "%s R=%d mode %d differs" % (name, R, mode)
-                assert m.last_stats.rays == rays and m.last_stats.samples == w * h * spp and m.last_stats.exchange_ms > 0
+                # every GPU traces its own primary rays (the cached primary hit lives in a path slot), so the ray total grows with R
+                assert m.last_stats.rays >= rays and m.last_stats.samples == w * h * spp and m.last_stats.exchange_ms > 0
         # GPU-side ingest on every GPU + device PNG stage
         cam = m.load_scene_gpu(SCENES, "cornell-box"); m.build_bvh()
         w, h, spp, base, _ = single["cornell-box"]
