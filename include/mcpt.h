@@ -111,9 +111,13 @@ enum { MCPT_FLAG_COUNT = 1,            /* count node visits / triangle tests (sl
        /* Quality extensions.  OFF by default: with either of them the image is no longer the reference's. */
        MCPT_FLAG_JITTER = 8,          /* every sample's primary ray goes through its own Philox-drawn point of the pixel (the reference
                                          shoots all samples through the pixel's corner, MTPC/pathTracing.cpp:305-308): anti-aliasing */
-       MCPT_FLAG_ANYHIT_SHADOW = 16   /* a light sample is visible iff NOTHING lies between the shading point and it (the reference:
+       MCPT_FLAG_ANYHIT_SHADOW = 16,  /* a light sample is visible iff NOTHING lies between the shading point and it (the reference:
                                          iff the closest hit carries the light's material, MTPC/pathTracing.cpp:212-215, so the
-                                         far side of a convex light counts as visible through its near side) */ };
+                                         far side of a convex light counts as visible through its near side) */
+       MCPT_FLAG_MIS_BALANCE = 32     /* a physically based estimator instead of the reference's lobe partition (MTPC/pathTracing.cpp:
+                                         171-262): Lambert + normalised Phong on the normalised shading normal, uniform area sampling
+                                         of every light and BSDF sampling combined with the balance heuristic, any-hit visibility
+                                         (csrc/shade.cuh "MCPT_FLAG_MIS_BALANCE"); implies ANYHIT_SHADOW, no primary-hit reuse */ };
 
 /* Number of sample chunks a render is always cut into (chunk k = samples [k*spp/C, (k+1)*spp/C)); GPU r of R in
  * {1,2,4,8} owns chunks [r*C/R,(r+1)*C/R).  Every chunk is accumulated sequentially into its own plane and the planes are

@@ -7,7 +7,7 @@ LIB_PATH = os.environ.get("MCPT_LIB") or os.path.join(HERE, "libmcpt.so")   # MC
 
 NUM_CHUNKS = 64
 MODE_MEGAKERNEL, MODE_WAVEFRONT = 0, 1
-FLAG_COUNT, FLAG_NO_PRIMARY_REUSE, FLAG_NO_SHADOW_EARLY_OUT, FLAG_JITTER, FLAG_ANYHIT_SHADOW = 1, 2, 4, 8, 16
+FLAG_COUNT, FLAG_NO_PRIMARY_REUSE, FLAG_NO_SHADOW_EARLY_OUT, FLAG_JITTER, FLAG_ANYHIT_SHADOW, FLAG_MIS_BALANCE = 1, 2, 4, 8, 16, 32
 
 
 class Material(C.Structure):

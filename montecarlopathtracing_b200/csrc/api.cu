@@ -608,6 +608,7 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
     if (mode != MCPT_MODE_MEGAKERNEL && mode != MCPT_MODE_WAVEFRONT) return fail_arg("render: unknown mode");
     if (getenv("MCPT_NO_SHADOW_EARLY_OUT")) flags |= MCPT_FLAG_NO_SHADOW_EARLY_OUT;   // developer A/B switch (same image either way)
     if (flags & MCPT_FLAG_JITTER) flags |= MCPT_FLAG_NO_PRIMARY_REUSE;                  // every sample has its own primary ray
+    if (flags & MCPT_FLAG_MIS_BALANCE) flags |= MCPT_FLAG_ANYHIT_SHADOW | MCPT_FLAG_NO_PRIMARY_REUSE;
     const int nch = ce - cb;
     const size_t plane = (size_t)width * height * 3;
     CU(grow(c->d_planes, c->planes_cap, sizeof(float) * plane * nch));

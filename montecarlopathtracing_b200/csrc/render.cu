@@ -48,7 +48,7 @@ int launch_raygen(const DCamera& cam, float* d_dirs, cudaStream_t stream) {
 // a pure function of (seed, pixel, sample) and of the fixed chunk tree (DESIGN.md "determinism").
 enum { PH_PRIMARY = -2, PH_NEWSAMPLE = -1 };
 
-template <bool COUNT, bool REUSE_PRIMARY>
+template <bool COUNT, bool REUSE_PRIMARY, bool MIS>
 __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
     const DeviceScene& sc = P.scene;
     const int W = P.cam.width, H = P.cam.height;
@@ -82,6 +82,8 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
         float3 beta = f3(1.f, 1.f, 1.f), L = f3(0.f, 0.f, 0.f), pend = f3(0.f, 0.f, 0.f), wnext = f3(1.f, 1.f, 1.f);
         float3 ro = cam_o, rd = cam_d; float rtmax = 3.0e38f;
         int phase = PH_NEWSAMPLE, lobe = LOBE_DIFFUSE, light_mat = -1;
+        MisFrame F; F.n = F.r = F.kd = F.ks = f3(0.f, 0.f, 0.f); F.pd = 1.f; F.Ns = 1.f;
+        float pdf_b = 0.f;
         unsigned bounce = 0;
         bool done = false;
 
@@ -94,6 +96,7 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
             const int li = sc.materials[m].light_id;
             if (li >= 0) { finish_sample(f3(sc.lights[li].radiance[0], sc.lights[li].radiance[1], sc.lights[li].radiance[2])); return; }
             make_vertex(sc, h, prim_d, vx);
+            if (MIS) F = mis_frame(sc, vx);
             beta = f3(1.f, 1.f, 1.f); L = f3(0.f, 0.f, 0.f); bounce = 0; phase = 0;
         };
 
@@ -118,14 +121,17 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
                 } else if (phase < nl) {
                     const float4 u = philox_uniform4(bounce, STREAM_LIGHT0 + phase, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
                     const DLight& Lt = sc.lights[phase];
-                    if (sample_light(sc, Lt, vx, u, ro, rd, rtmax, pend, anyhit)) { light_mat = Lt.mat_id; have_ray = true; }
+                    const bool ok = MIS ? sample_light_mis(sc, Lt, F, vx, u, ro, rd, rtmax, pend) : sample_light(sc, Lt, vx, u, ro, rd, rtmax, pend, anyhit);
+                    if (ok) { light_mat = Lt.mat_id; have_ray = true; }
                     else phase++;
                 } else {
                     const float4 u = philox_uniform4(bounce, STREAM_PATH, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
                     if (u.x < MCPT_P_RR && bounce + 1 < MCPT_MAX_DEPTH) {   // russian_Roulette (:3-11,:240)
-                        next_ray(sc, vx, u, bounce, P.seed_lo, P.seed_hi, pixel, (unsigned)s, ro, rd, lobe, wnext);
+                        bool ext = true;
+                        if (MIS) ext = next_ray_mis(sc, F, vx, u, bounce, P.seed_lo, P.seed_hi, pixel, (unsigned)s, ro, rd, lobe, wnext, pdf_b);
+                        else next_ray(sc, vx, u, bounce, P.seed_lo, P.seed_hi, pixel, (unsigned)s, ro, rd, lobe, wnext);
                         rtmax = 3.0e38f;
-                        have_ray = true;
+                        if (ext) have_ray = true; else finish_sample(L);
                     } else finish_sample(L);
                 }
             }
@@ -153,12 +159,14 @@ __global__ void __launch_bounds__(128) pt_megakernel(const RenderParams P) {
                 const int li = sc.materials[m].light_id;
                 const float3 bw = mul_rn(beta, wnext * (1.0f / MCPT_P_RR));
                 if (li >= 0) {   // diffuse rays drop emitters (NEE counted them, :247-253); specular/transmission keep them
-                    if (lobe != LOBE_DIFFUSE)
-                        L = add_rn(L, mul_rn(bw, f3(sc.lights[li].radiance[0], sc.lights[li].radiance[1], sc.lights[li].radiance[2])));
+                    const float3 Le = f3(sc.lights[li].radiance[0], sc.lights[li].radiance[1], sc.lights[li].radiance[2]);
+                    if (MIS) L = add_rn(L, mul_rn(bw, Le * mis_weight_bsdf_hit(sc, h.k, rd, h.t, sc.lights[li].area, pdf_b)));
+                    else if (lobe != LOBE_DIFFUSE) L = add_rn(L, mul_rn(bw, Le));
                     finish_sample(L);
                 } else {
                     beta = bw;
                     make_vertex(sc, h, rd, vx);
+                    if (MIS) F = mis_frame(sc, vx);
                     bounce++;
                     phase = 0;
                 }
@@ -320,10 +328,11 @@ int launch_megakernel(const RenderParams& P, int flags, cudaStream_t stream) {
     const long long blocks = (warps * 32 + tpb - 1) / tpb;
     if (blocks <= 0 || blocks > 0x7fffffffLL) return (int)cudaErrorInvalidConfiguration;
     const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
-    if (count && reuse) pt_megakernel<true, true><<<(unsigned)blocks, tpb, 0, stream>>>(P);
-    else if (count) pt_megakernel<true, false><<<(unsigned)blocks, tpb, 0, stream>>>(P);
-    else if (reuse) pt_megakernel<false, true><<<(unsigned)blocks, tpb, 0, stream>>>(P);
-    else pt_megakernel<false, false><<<(unsigned)blocks, tpb, 0, stream>>>(P);
+    if (flags & MCPT_FLAG_MIS_BALANCE) pt_megakernel<false, false, true><<<(unsigned)blocks, tpb, 0, stream>>>(P);
+    else if (count && reuse) pt_megakernel<true, true, false><<<(unsigned)blocks, tpb, 0, stream>>>(P);
+    else if (count) pt_megakernel<true, false, false><<<(unsigned)blocks, tpb, 0, stream>>>(P);
+    else if (reuse) pt_megakernel<false, true, false><<<(unsigned)blocks, tpb, 0, stream>>>(P);
+    else pt_megakernel<false, false, false><<<(unsigned)blocks, tpb, 0, stream>>>(P);
     return (int)cudaGetLastError();
 }
 

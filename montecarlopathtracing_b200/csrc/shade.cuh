@@ -163,4 +163,96 @@ __device__ __forceinline__ void next_ray(const DeviceScene& sc, const PathVertex
     ray_o = vx.p + ray_d * 0.01f;
 }
 
+// ---- MCPT_FLAG_MIS_BALANCE: a physically based estimator, NOT the reference's ---------------------------
+// The reference partitions light transport by lobe — next-event estimation for the diffuse lobe only, BSDF sampling for the
+// specular lobe only, no pdfs (quirks Q6-Q9) — which is why its veach-mis render is noisy on the plates.  This mode is the
+// textbook alternative: a Lambert + normalised-Phong BRDF  f = kd/pi + ks (Ns+2)/(2 pi) cos^Ns(alpha)  on the NORMALISED shading
+// normal turned toward the viewer, uniform area sampling of every light (one sample per light and vertex) and BSDF sampling
+// (lobe picked with probability |kd| / (|kd| + |ks|)), combined with the balance heuristic; any-hit visibility.  Same Philox
+// streams and Russian roulette as the parity mode.  oracle/mcpt_oracle.c has the FP64 twin (tests compare them pixel by pixel).
+struct MisFrame { float3 n, r, kd, ks; float pd, Ns; };
+__device__ __forceinline__ MisFrame mis_frame(const DeviceScene& sc, const PathVertex& vx) {
+    const DMaterial* m = &sc.materials[vx.mat];
+    MisFrame F;
+    F.n = normalize(vx.pn);
+    if (dot(F.n, vx.wo) < 0.0f) F.n = -F.n;
+    const float two_c = __fmul_rn(2.0f, dot(F.n, vx.wo));   // explicit roundings: both integrators must form the same bits
+    F.r = f3(__fmaf_rn(F.n.x, two_c, -vx.wo.x), __fmaf_rn(F.n.y, two_c, -vx.wo.y), __fmaf_rn(F.n.z, two_c, -vx.wo.z));
+    F.kd = vx.kd; F.ks = f3(m->ks[0], m->ks[1], m->ks[2]); F.Ns = m->Ns;
+    const float kdn = length(vx.kd), ksn = m->ks_norm;
+    F.pd = (kdn + ksn) > 0.0f ? kdn / (kdn + ksn) : 1.0f;
+    return F;
+}
+__device__ __forceinline__ float mis_lobe(const MisFrame& F, const float3 wi) { return powf(fmaxf(dot(F.r, wi), 0.0f), F.Ns); }
+__device__ __forceinline__ float3 mis_brdf(const MisFrame& F, const float lobe) {
+    const float sp = __fmul_rn(__fmul_rn(__fadd_rn(F.Ns, 2.0f), 0.5f / MCPT_PI), lobe);
+    return f3(__fmaf_rn(F.ks.x, sp, __fmul_rn(F.kd.x, 1.0f / MCPT_PI)), __fmaf_rn(F.ks.y, sp, __fmul_rn(F.kd.y, 1.0f / MCPT_PI)),
+              __fmaf_rn(F.ks.z, sp, __fmul_rn(F.kd.z, 1.0f / MCPT_PI)));
+}
+__device__ __forceinline__ float mis_pdf_bsdf(const MisFrame& F, const float cosi, const float lobe) {
+    const float sp = __fmul_rn(__fmul_rn(__fmul_rn(__fsub_rn(1.0f, F.pd), __fadd_rn(F.Ns, 1.0f)), 0.5f / MCPT_PI), lobe);
+    return __fmaf_rn(__fmul_rn(F.pd, cosi), 1.0f / MCPT_PI, sp);
+}
+// solid-angle pdf with which light L's area sampling picks the point at distance `dist` along w on a surface of normal ng
+__device__ __forceinline__ float mis_pdf_light(const float area, const float dist, const float cosl) {
+    return __fdiv_rn(__fmul_rn(dist, dist), __fmul_rn(area, cosl));
+}
+
+// contrib = f cos Le / pdf_L * pdf_L / (pdf_L + pdf_B): the caller multiplies by the throughput and the any-hit visibility
+__device__ __forceinline__ bool sample_light_mis(const DeviceScene& sc, const DLight& L, const MisFrame& F, const PathVertex& vx, const float4 u,
+                                                 float3& ray_o, float3& ray_d, float& ray_tmax, float3& contrib) {
+    const float rnd = u.x * L.area;
+    const float* cdf = sc.light_cdf + L.first;
+    int lo = 0, hi = L.count - 1;     // first j with rnd < cdf[j] (the last triangle catches rnd == area after rounding)
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (rnd < __ldg(&cdf[mid])) hi = mid; else lo = mid + 1; }
+    const LightTri* lt = &sc.light_tris[L.first + lo];
+    const float3 A = f3(__ldg(&lt->p0n0x)), B = f3(__ldg(&lt->p1n0y)), C = f3(__ldg(&lt->p2n0z));
+    const float su = sqrtf(u.y);
+    const float b0 = __fsub_rn(1.0f, su), b1 = __fmul_rn(su, __fsub_rn(1.0f, u.z)), b2 = __fmul_rn(su, u.z);
+    const float3 xl = f3(__fmaf_rn(C.x, b2, __fmaf_rn(B.x, b1, __fmul_rn(A.x, b0))), __fmaf_rn(C.y, b2, __fmaf_rn(B.y, b1, __fmul_rn(A.y, b0))),
+                         __fmaf_rn(C.z, b2, __fmaf_rn(B.z, b1, __fmul_rn(A.z, b0))));   // uniform over the triangle
+    const float3 ng = normalize(cross(B - A, C - A));
+    const float3 dv = xl - vx.p;
+    const float dist = length(dv);
+    const float3 w = dv * (1.0f / dist);
+    const float cosi = dot(F.n, w), cosl = fabsf(dot(ng, w));
+    if (!(cosi > 0.0f) || !(cosl > 1.0e-6f) || !(dist > 0.0f)) return false;
+    const float lobe = mis_lobe(F, w);
+    const float g = __fdiv_rn(cosi, __fadd_rn(mis_pdf_light(L.area, dist, cosl), mis_pdf_bsdf(F, cosi, lobe)));
+    contrib = mis_brdf(F, lobe) * f3(L.radiance[0], L.radiance[1], L.radiance[2]) * g;
+    if (!(contrib.x != 0.0f || contrib.y != 0.0f || contrib.z != 0.0f)) return false;
+    ray_o = vx.p + w * 0.01f; ray_d = w;
+    ray_tmax = (dist - 0.01f) * 0.9999f;
+    return true;
+}
+// BSDF sampling; weight = f cos / pdf_B, pdf_b = pdf_B of the sampled direction (< 0: the reference's delta refraction branch,
+// whose emission is counted in full).  Returns false when the sampled direction leaves the hemisphere of n (the path ends).
+__device__ __forceinline__ bool next_ray_mis(const DeviceScene& sc, const MisFrame& F, const PathVertex& vx, const float4 u, const unsigned bounce,
+                                             const unsigned seed_lo, const unsigned seed_hi, const unsigned pixel, const unsigned sample,
+                                             float3& ray_o, float3& ray_d, int& lobe_tag, float3& weight, float& pdf_b) {
+    if (sc.materials[vx.mat].Ni > 1.0f) {
+        next_ray(sc, vx, u, bounce, seed_lo, seed_hi, pixel, sample, ray_o, ray_d, lobe_tag, weight);
+        pdf_b = -1.0f;
+        return true;
+    }
+    if (u.y < F.pd) { ray_d = brdf_sample(F.n, LOBE_DIFFUSE, F.Ns, u.z, u.w); lobe_tag = LOBE_DIFFUSE; }
+    else { ray_d = brdf_sample(F.r, LOBE_SPECULAR, F.Ns, u.z, u.w); lobe_tag = LOBE_SPECULAR; }
+    const float cosi = dot(F.n, ray_d);
+    if (!(cosi > 0.0f)) return false;
+    const float lobe = mis_lobe(F, ray_d);
+    pdf_b = mis_pdf_bsdf(F, cosi, lobe);
+    if (!(pdf_b > 0.0f)) return false;
+    weight = mis_brdf(F, lobe) * __fdiv_rn(cosi, pdf_b);
+    ray_o = vx.p + ray_d * 0.01f;
+    return true;
+}
+// Balance-heuristic weight of an emitter found by BSDF sampling: hit triangle k (a light of area `area`) at distance t along d.
+__device__ __forceinline__ float mis_weight_bsdf_hit(const DeviceScene& sc, const int k, const float3 d, const float t, const float area, const float pdf_b) {
+    if (pdf_b < 0.0f) return 1.0f;
+    const float3 ng = normalize(cross(f3(__ldg(&sc.tri[k].e1f)), f3(__ldg(&sc.tri[k].e2))));
+    const float cosl = fabsf(dot(ng, d));
+    if (!(cosl > 1.0e-6f)) return 1.0f;
+    return __fdiv_rn(pdf_b, __fadd_rn(pdf_b, mis_pdf_light(area, t, cosl)));
+}
+
 }  // namespace mcpt

@@ -81,7 +81,7 @@ __device__ __forceinline__ void push_ray(const bool pred, const WfBuffers& B, un
 #ifndef MCPT_SHADE_MIN_CTAS
 #define MCPT_SHADE_MIN_CTAS 4
 #endif
-template <bool REUSE_PRIMARY>
+template <bool REUSE_PRIMARY, bool MIS>
 __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const RenderParams P, const WfBuffers B, const int iter) {
     const DeviceScene& sc = P.scene;
     const int W = P.cam.width, H = P.cam.height;
@@ -191,8 +191,11 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
                     const int m = __float_as_int(__ldg(&sc.tri[h.k].v0m).w);
                     const int li = sc.materials[m].light_id;
                     if (li >= 0) {   // diffuse rays drop emitters (NEE counted them, :247-253); specular/transmission keep them
-                        if (lobe != LOBE_DIFFUSE)
-                            L = add_rn(L, mul_rn(beta, f3(sc.lights[li].radiance[0], sc.lights[li].radiance[1], sc.lights[li].radiance[2])));
+                        const float3 Le = f3(sc.lights[li].radiance[0], sc.lights[li].radiance[1], sc.lights[li].radiance[2]);
+                        if (MIS) {   // balance heuristic against the light's own area sampling (rd.w = pdf of the BSDF sample)
+                            const float wb = mis_weight_bsdf_hit(sc, h.k, f3(rd_in.x, rd_in.y, rd_in.z), h.t, sc.lights[li].area, rd_in.w);
+                            L = add_rn(L, mul_rn(beta, Le * wb));
+                        } else if (lobe != LOBE_DIFFUSE) L = add_rn(L, mul_rn(beta, Le));
                         finish_sample(L);
                     } else {
                         const float4 r4 = rd_in;
@@ -222,12 +225,15 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
     // ---- emission: the whole warp walks the lights together so every push is one ballot + one atomic ----
     PathVertex vx; vx.mat = 0; vx.k = 0; vx.t = 0.f; vx.p = vx.pn = vx.kd = vx.wo = f3(0.f, 0.f, 0.f);
     if (have_vertex) { make_vertex(sc, hv, vdir, vx); __stcg(&B.vis[slot], 0u); }
+    MisFrame F;
+    if (MIS && have_vertex) F = mis_frame(sc, vx);
+    float pdf_b = 0.f;
     for (int l = 0; l < nl; l++) {
         bool ok = false;
         float3 o = f3(0.f, 0.f, 0.f), d = o, contrib = o; float tmax = 0.f;
         if (have_vertex) {
             const float4 u = philox_uniform4(bounce, STREAM_LIGHT0 + l, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
-            ok = sample_light(sc, sc.lights[l], vx, u, o, d, tmax, contrib, anyhit);
+            ok = MIS ? sample_light_mis(sc, sc.lights[l], F, vx, u, o, d, tmax, contrib) : sample_light(sc, sc.lights[l], vx, u, o, d, tmax, contrib, anyhit);
             if (ok) { const float3 bp = mul_rn(beta, contrib); __stcg(&B.pend[(size_t)l * B.n_slots + slot], make_float4(bp.x, bp.y, bp.z, 0.f)); }
         }
         push_ray(ok, B, tail, o, d, tmax, (unsigned)slot | ((unsigned)(l + 1) << WF_ID_BITS), push_sh, l);
@@ -240,9 +246,9 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
             const float4 u = philox_uniform4(bounce, STREAM_PATH, P.seed_lo, P.seed_hi, pixel, (unsigned)s);
             if (u.x < MCPT_P_RR && bounce + 1 < MCPT_MAX_DEPTH) {   // russian_Roulette (:3-11,:240)
                 float3 wnext;
-                next_ray(sc, vx, u, bounce, P.seed_lo, P.seed_hi, pixel, (unsigned)s, o, d, lobe, wnext);
-                beta = mul_rn(beta, wnext * (1.0f / MCPT_P_RR));
-                rd = d; ext = true;
+                if (MIS) ext = next_ray_mis(sc, F, vx, u, bounce, P.seed_lo, P.seed_hi, pixel, (unsigned)s, o, d, lobe, wnext, pdf_b);
+                else { next_ray(sc, vx, u, bounce, P.seed_lo, P.seed_hi, pixel, (unsigned)s, o, d, lobe, wnext); ext = true; }
+                if (ext) { beta = mul_rn(beta, wnext * (1.0f / MCPT_P_RR)); rd = d; }
             }
             has_extend = ext;
         }
@@ -255,7 +261,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
             __stcg(&B.sum_s[slot], make_float4(sum.x, sum.y, sum.z, __int_as_float(s)));
             if (have_vertex) {
                 __stcg(&B.L[slot], make_float4(L.x, L.y, L.z, 0.f));
-                if (has_extend) __stcg(&B.rd[slot], make_float4(rd.x, rd.y, rd.z, 0.f));
+                if (has_extend) __stcg(&B.rd[slot], make_float4(rd.x, rd.y, rd.z, pdf_b));
             }
             if (store_hit0) __stcg(&B.hit0[slot], make_float4(hit0.t, hit0.u, hit0.v, __int_as_float(hit0.k)));
         }
@@ -503,7 +509,7 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
     WF_CU(cudaEventRecord(ev_fork, stream));
     for (int k = 1; k < pipes; k++) WF_CU(cudaStreamWaitEvent(pp[k].st, ev_fork, 0));
 
-    const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE);
+    const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE), mis = (flags & MCPT_FLAG_MIS_BALANCE) != 0;
     const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 12) / pipes;   // CTAs of 4 warps, shared by the pipes
     const int refill_min = env_int("MCPT_REFILL_MIN", 12), leaf_min = env_int("MCPT_LEAF_MIN", 1),
               block_min = env_int("MCPT_BLOCK_MIN", 1), node_steps = env_int("MCPT_NODE_STEPS", MCPT_WIDE ? 2 : 4);
@@ -525,8 +531,9 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
             if (q.done) continue;
             any = true;
             for (int iter = b * batch; iter < (b + 1) * batch; iter++) {
-                if (reuse) wf_shade<true><<<q.shade_blocks, 256, 0, q.st>>>(P, q.B, iter);
-                else wf_shade<false><<<q.shade_blocks, 256, 0, q.st>>>(P, q.B, iter);
+                if (mis) wf_shade<false, true><<<q.shade_blocks, 256, 0, q.st>>>(P, q.B, iter);
+                else if (reuse) wf_shade<true, false><<<q.shade_blocks, 256, 0, q.st>>>(P, q.B, iter);
+                else wf_shade<false, false><<<q.shade_blocks, 256, 0, q.st>>>(P, q.B, iter);
                 while (H.trace_events.size() < 2 * (size_t)(n_timed + 1)) {   // one event pair per wf_trace launch, reused across renders
                     cudaEvent_t ev; WF_CU(cudaEventCreate(&ev));
                     H.trace_events.push_back(ev);

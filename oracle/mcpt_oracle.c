@@ -445,6 +445,119 @@ static V3 shade(const orc_scene* S, const Isect* p, V3 wo, Rng* g, int bounce) {
     return vadd(L_dir, L_indir);
 }
 
+
+/* ---- MCPT_FLAG_MIS_BALANCE: FP64 twin of the CUDA integrator's physically based mode (csrc/shade.cuh) -------------------------
+ * NOT the reference's estimator: Lambert + normalised Phong on the normalised shading normal turned toward the viewer, uniform
+ * area sampling of every light + BSDF sampling combined with the balance heuristic, any-hit visibility.  Same Philox streams. */
+enum { ORC_MIS_BSDF_ONLY = 64, ORC_MIS_NEE_ONLY = 128 };   /* test-only variants: each strategy alone (weights 1 / 0) */
+typedef struct { V3 n, r, kd, ks; double pd, Ns; } MisFrame;
+static double mis_lobe(const MisFrame* F, V3 wi) { double c = vdot(F->r, wi); return pow(c > 0 ? c : 0, F->Ns); }
+static V3 mis_brdf(const MisFrame* F, double lobe) {
+    double sp = (F->Ns + 2) * (0.5 / ORC_PI) * lobe;
+    return v3(F->kd.x / ORC_PI + F->ks.x * sp, F->kd.y / ORC_PI + F->ks.y * sp, F->kd.z / ORC_PI + F->ks.z * sp);
+}
+static double mis_pdf_bsdf(const MisFrame* F, double cosi, double lobe) {
+    return F->pd * cosi / ORC_PI + (1 - F->pd) * (F->Ns + 1) * (0.5 / ORC_PI) * lobe;
+}
+static V3 texel_or_kd(const orc_scene* S, const Tri* f, const mcpt_material* m, V3 p) {
+    if (m->tex_id < 0) return v3(m->kd[0], m->kd[1], m->kd[2]);
+    V3 gc = bary_of(f, p);
+    double row = f->uv[0] * gc.x + f->uv[2] * gc.y + f->uv[4] * gc.z;
+    double col = f->uv[1] * gc.x + f->uv[3] * gc.y + f->uv[5] * gc.z;
+    double irow = row - floor(row), icol = col - floor(col);
+    int H = S->tex_h[m->tex_id], W = S->tex_w[m->tex_id];
+    int r = (int)(irow * H), c = (int)(icol * W);
+    if (r > H - 1) r = H - 1;
+    if (c > W - 1) c = W - 1;
+    const uint8_t* px = S->tex[m->tex_id] + ((size_t)r * W + c) * 3;
+    return v3((double)px[2] / 255, (double)px[1] / 255, (double)px[0] / 255);
+}
+/* radiance arriving along -wo at hit p; pdf_b = pdf of the BSDF sample that found p (< 0: camera ray or delta branch) */
+static V3 shade_mis(const orc_scene* S, const Isect* p, Ray in, double pdf_b, Rng* g, int bounce) {
+    const Tri* f = &S->tri[p->k];
+    V3 wo = vneg(in.d);
+    if (S->mat_light[f->mat] >= 0) {
+        int li = S->mat_light[f->mat];
+        const double* le = S->light[li].radiance;
+        double w = 1;
+        if (pdf_b >= 0) {
+            V3 ng = vnormalize(vcross(vsub(f->v2, f->v1), vsub(f->v3, f->v1)));
+            double cosl = fabs(vdot(ng, in.d));
+            if (cosl > 1e-6) w = pdf_b / (pdf_b + p->t * p->t / (S->light_area[li] * cosl));
+            if (g->flags & ORC_MIS_BSDF_ONLY) w = 1;   /* validation variants of the tests: one strategy alone must agree */
+            if (g->flags & ORC_MIS_NEE_ONLY) w = 0;
+        }
+        return v3(le[0] * w, le[1] * w, le[2] * w);
+    }
+    const mcpt_material* m = &S->mat[f->mat];
+    MisFrame F;
+    F.kd = texel_or_kd(S, f, m, p->p);
+    F.ks = v3(m->ks[0], m->ks[1], m->ks[2]); F.Ns = m->Ns;
+    F.n = vnormalize(p->pn);
+    if (vdot(F.n, wo) < 0) F.n = vneg(F.n);
+    F.r = vsub(vmul(F.n, 2 * vdot(F.n, wo)), wo);
+    double kdn = vnorm(F.kd), ksn = vnorm(F.ks);
+    F.pd = (kdn + ksn) > 0 ? kdn / (kdn + ksn) : 1;
+    V3 L = v3(0, 0, 0);
+    for (int i = 0; i < S->n_light; i++) {
+        double u[4];
+        draw4(g, bounce, STREAM_LIGHT0 + i, u);
+        double A = S->light_area[i], rnd = u[0] * A;
+        int sel = S->light_ntri[i] - 1;
+        for (int j = 0; j < S->light_ntri[i]; j++) if (rnd < S->light_cdf[i][j]) { sel = j; break; }
+        const Tri* sf = &S->obj_tri[S->light_tris[i][sel]];
+        double su = sqrt(u[1]);
+        V3 xl = vadd(vadd(vmul(sf->v1, 1 - su), vmul(sf->v2, su * (1 - u[2]))), vmul(sf->v3, su * u[2]));
+        V3 ng = vnormalize(vcross(vsub(sf->v2, sf->v1), vsub(sf->v3, sf->v1)));
+        V3 dv = vsub(xl, p->p);
+        double dist = vnorm(dv);
+        V3 w = vdiv(dv, dist);
+        double cosi = vdot(F.n, w), cosl = fabs(vdot(ng, w));
+        if (!(cosi > 0) || !(cosl > 1e-6) || !(dist > 0)) continue;
+        double lobe = mis_lobe(&F, w);
+        double gg = cosi / (dist * dist / (A * cosl) + mis_pdf_bsdf(&F, cosi, lobe));
+        if (g->flags & ORC_MIS_NEE_ONLY) gg = cosi / (dist * dist / (A * cosl));
+        if (g->flags & ORC_MIS_BSDF_ONLY) continue;
+        V3 fr = mis_brdf(&F, lobe);
+        const double* le = S->light[i].radiance;
+        V3 c = v3(fr.x * le[0] * gg, fr.y * le[1] * gg, fr.z * le[2] * gg);
+        if (c.x == 0 && c.y == 0 && c.z == 0) continue;
+        Ray rl; rl.o = vadd(p->p, vmul(w, 0.01)); rl.d = w;
+        Isect inter;
+        g->n_shadow++;
+        if (ray_intersect(S, &rl, &inter) && inter.t < (dist - 0.01) * 0.9999) continue;   /* any-hit visibility */
+        L = vadd(L, c);
+    }
+    double u[4];
+    draw4(g, bounce, STREAM_PATH, u);
+    if (u[0] < ORC_P_RR && bounce + 1 < ORC_MAX_DEPTH) {
+        Ray r; V3 weight; double pb;
+        if (m->Ni > 1) {   /* the reference's delta refraction branch, emission counted in full */
+            int type;
+            r = next_ray(S, p, wo, F.kd, m, g, bounce, &type);
+            weight = type == RT_DIFFUSE ? F.kd : type == RT_SPECULAR ? F.ks : v3(1, 1, 1);
+            pb = -1;
+        } else {
+            V3 d = u[1] < F.pd ? brdf_sample(F.n, RT_DIFFUSE, F.Ns, u[2], u[3]) : brdf_sample(F.r, RT_SPECULAR, F.Ns, u[2], u[3]);
+            double cosi = vdot(F.n, d);
+            if (!(cosi > 0)) return L;
+            double lobe = mis_lobe(&F, d);
+            pb = mis_pdf_bsdf(&F, cosi, lobe);
+            if (!(pb > 0)) return L;
+            V3 fr = mis_brdf(&F, lobe);
+            weight = vmul(fr, cosi / pb);
+            r.o = vadd(p->p, vmul(d, 0.01)); r.d = d;
+        }
+        Isect ret;
+        g->n_extend++;
+        if (ray_intersect(S, &r, &ret)) {
+            V3 Li = vdiv(shade_mis(S, &ret, r, pb, g, bounce + 1), ORC_P_RR);
+            L.x += weight.x * Li.x; L.y += weight.y * Li.y; L.z += weight.z * Li.z;
+        }
+    }
+    return L;
+}
+
 /* generateImg, MTPC/pathTracing.cpp:274-331.  Samples [s0,s1) of spp are integrated; img gets their SUM / spp.
  * counts3 = {primary, shadow, extend} closest-hit queries. */
 MCPT_API void orc_render_flags(const orc_scene* S, const mcpt_camera* cam, int width, int height, int spp, int s0, int s1,
@@ -486,7 +599,7 @@ MCPT_API void orc_render_flags(const orc_scene* S, const mcpt_camera* cam, int w
                 Isect ret;
                 np++;
                 if (ray_intersect(S, &ray, &ret)) {
-                    V3 rad = shade(S, &ret, vneg(ray.d), &g, 0);
+                    V3 rad = (flags & MCPT_FLAG_MIS_BALANCE) ? shade_mis(S, &ret, ray, -1.0, &g, 0) : shade(S, &ret, vneg(ray.d), &g, 0);
                     acc[0] += rad.x / spp; acc[1] += rad.y / spp; acc[2] += rad.z / spp;
                     ns += g.n_shadow; ne += g.n_extend;
                 }

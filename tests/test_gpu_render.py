@@ -363,7 +363,8 @@ def test_render_dist_on_one_rank_equals_render(gpu_ctx, scenes):
 
 
 @pytest.mark.parametrize("name,flags", [("cornell-box", M.FLAG_JITTER), ("veach-mis", M.FLAG_ANYHIT_SHADOW),
-                                        ("veach-mis", M.FLAG_JITTER | M.FLAG_ANYHIT_SHADOW)])
+                                        ("veach-mis", M.FLAG_JITTER | M.FLAG_ANYHIT_SHADOW), ("cornell-box", M.FLAG_MIS_BALANCE),
+                                        ("veach-mis", M.FLAG_MIS_BALANCE | M.FLAG_JITTER)])
 def test_quality_flags_match_their_oracle_twins(gpu_ctx, oracle, scenes, name, flags):
     """MCPT_FLAG_JITTER / MCPT_FLAG_ANYHIT_SHADOW (off by default) against the CPU twins fed the same Philox
     numbers: same tolerance as the parity-mode pixel test; both integrators bit-identical; and the image really changed."""
@@ -373,7 +374,16 @@ def test_quality_flags_match_their_oracle_twins(gpu_ctx, oracle, scenes, name, f
     w, h, spp = 96, 72, 8
     img = gpu_ctx.render(s.camera, spp, w, h, mode=M.MODE_WAVEFRONT, flags=flags)
     ref, _ = oracle.OracleScene(s.desc).render(s.camera, spp, w, h, seed=77, flags=flags)
-    close = (np.abs(img - ref) <= 2e-3 * np.abs(ref) + 1e-4).all(axis=2).mean()
-    assert close >= 0.985, "only %.4f of pixels match the flagged oracle" % close
-    assert np.array_equal(img, gpu_ctx.render(s.camera, spp, w, h, mode=M.MODE_MEGAKERNEL, flags=flags))
+    # veach-mis under MIS evaluates cos^Ns(alpha) with Ns up to 1e5: FP32 holds 1 - cos(alpha) ~ 1e-5 to ~1 %, so the per-pixel
+    # tolerance is 2 % there (and the mean image is checked to 1 %); everything else keeps the parity-mode tolerance of 2e-3
+    loose = name == "veach-mis" and (flags & M.FLAG_MIS_BALANCE)
+    rtol = 2e-2 if loose else 2e-3
+    close = (np.abs(img - ref) <= rtol * np.abs(ref) + 1e-4).all(axis=2).mean()
+    assert close >= (0.95 if loose else 0.985), "only %.4f of pixels match the flagged oracle" % close
+    assert np.all(np.abs(np.minimum(img, 4).mean(axis=(0, 1)) - np.minimum(ref, 4).mean(axis=(0, 1))) <= 0.01 * np.minimum(ref, 4).mean(axis=(0, 1)))
+    mega = gpu_ctx.render(s.camera, spp, w, h, mode=M.MODE_MEGAKERNEL, flags=flags)
+    if flags & M.FLAG_MIS_BALANCE:   # the MIS math is not rounding-controlled end to end: a few pixels differ in the last bits
+        assert np.allclose(img, mega, rtol=2e-5, atol=1e-7) and (img != mega).any(axis=2).mean() < 0.05
+    else:
+        assert np.array_equal(img, mega)
     assert not np.array_equal(img, gpu_ctx.render(s.camera, spp, w, h))
