@@ -26,4 +26,22 @@ timeout 600 ncu --set full --import-source on --clock-control none --kernel-name
 for lib in sstack stop; do
   MCPT_LIB=$PWD/montecarlopathtracing_b200/libmcpt_$lib.so timeout 600 ncu --set full --clock-control none --kernel-name regex:wf_trace --launch-skip 120 --launch-count 1 -f -o gpurun_out/r2_wf_trace_$lib python tools/profile_render.py --workload cornell-box-1024x1024 --spp 256 > gpurun_out/r2_wf_trace_$lib.log 2>&1; echo "full wf_trace $lib rc=$?"
 done
-ls -la gpurun_out/*.ncu-rep | awk '{print $5, $9}'
+# summarise on the box (the raw reports exceed what gpurun copies back), then drop them
+for f in gpurun_out/r2_wf_trace_*.ncu-rep gpurun_out/r2_wf_shade_*.ncu-rep gpurun_out/r2_megakernel.ncu-rep; do
+  b=${f%.ncu-rep}
+  python tools/ncu_summary.py metrics $f ${b}_ncu.md
+  python tools/ncu_summary.py lines $f ${b}_lines.md 2>/dev/null
+done
+python tools/ncu_summary.py source gpurun_out/r2_wf_trace_cornell-box-1024x1024.ncu-rep gpurun_out/r2_wf_trace_cornell-box-1024x1024_source.md
+python tools/ncu_summary.py metrics gpurun_out/r2_all_cornell-box.ncu-rep gpurun_out/r2_all_cornell-box_ncu.md
+python tools/ncu_summary.py metrics gpurun_out/r2_all_synthetic-1M.ncu-rep gpurun_out/r2_all_synthetic-1M_ncu.md
+python tools/roofline_table.py gpurun_out/r2_roofline.md gpurun_out/r2_all_cornell-box.ncu-rep:cornell-box gpurun_out/r2_all_synthetic-1M.ncu-rep:synthetic-1M \
+  gpurun_out/r2_wf_trace_cornell-box-1024x1024.ncu-rep:cornell-box-mid-render gpurun_out/r2_wf_shade_cornell-box-1024x1024.ncu-rep:cornell-box-mid-render \
+  gpurun_out/r2_wf_trace_veach-mis-1200x900.ncu-rep:veach-mis-mid-render gpurun_out/r2_wf_shade_veach-mis-1200x900.ncu-rep:veach-mis-mid-render \
+  gpurun_out/r2_wf_trace_synthetic-5M-1920x1080.ncu-rep:synthetic-5M-mid-render gpurun_out/r2_wf_shade_synthetic-5M-1920x1080.ncu-rep:synthetic-5M-mid-render \
+  gpurun_out/r2_megakernel.ncu-rep:cornell-box-megakernel gpurun_out/r2_wf_trace_sstack.ncu-rep:variant-smem-stack gpurun_out/r2_wf_trace_stop.ncu-rep:variant-smem-top256
+rm -f gpurun_out/*.ncu-rep
+# the default bench line and the reference arm, as the driver runs them
+python bench.py --steps 3 --warmup 3 > gpurun_out/z_bench.json 2> gpurun_out/z_bench.err; echo "bench rc=$?"; tail -2 gpurun_out/z_bench.err
+python bench.py --impl reference --steps 1 --warmup 0 > gpurun_out/z_bench_ref.json 2> gpurun_out/z_bench_ref.err; echo "ref rc=$?"
+du -sh gpurun_out
