@@ -42,7 +42,7 @@ SUB_RECORDS = ["cornell-box-1024x1024-spp256", "veach-mis-1200x900-spp100", "syn
 CPU_SAMPLE = {"cornell-box-3840x2160-spp1024": (384, 216, 16), "cornell-box-1024x1024-spp256": (192, 192, 32),
               "veach-mis-1200x900-spp100": (160, 120, 12)}
 # sources that define the profiled kernels: profiles/kernel_metrics.json is only believed while their hash matches
-KERNEL_SOURCES = ["wavefront.cu", "trace.cuh", "shade.cuh", "render.cu", "device_types.cuh", "vecmath.cuh", "philox.cuh", "quant.cuh"]
+KERNEL_SOURCES = ["wavefront.cu", "trace.cuh", "shade.cuh", "exact.cuh", "render.cu", "device_types.cuh", "vecmath.cuh", "philox.cuh", "quant.cuh"]
 
 
 def peaks():
