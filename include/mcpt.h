@@ -225,6 +225,18 @@ MCPT_API int mcpt_render(mcpt_ctx* ctx, const mcpt_camera* cam, int width, int h
  * buffer png_out (capacity >= mcpt_png_size(width, height)). */
 MCPT_API int64_t mcpt_png_size(int width, int height);
 MCPT_API int mcpt_encode_png(mcpt_ctx* ctx, const float* d_rgb, int width, int height, uint8_t* png_out, int64_t capacity);
+/* The same stage for callers that must not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * (code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc cannot call
+ * mcpt_encode_png, which grows a per-context device buffer).  Needs no mcpt_ctx; calls no cudaMalloc, cudaFree or allocating
+ * library routine: the device-side scratch (checksum accumulators, cleared every call, + the encoded file) is one file-scope
+ * __device__ array of MCPT_PNG_STATIC_BYTES that every GPU loading the library holds until exit.  Images whose encoded size +
+ * 256 B exceeds it (larger than about 1920 x 1080) are rejected with MCPT_ERR_ARG.  d_rgb: DEVICE image on `device`; png_out:
+ * host or device buffer of capacity >= mcpt_png_size(); cuda_stream: the caller's stream (NULL = the legacy default stream), which
+ * the call synchronises.  Same bytes as mcpt_encode_png.  All calls on a device share the array: calls that overlap on the
+ * GPU (other streams or threads) race; serialise them. */
+#define MCPT_PNG_STATIC_BYTES (8 << 20)
+MCPT_API int mcpt_encode_png_static(int device, const float* d_rgb, int width, int height, uint8_t* png_out, int64_t capacity,
+                                    void* cuda_stream);
 /* Seam 3 + output stage: render, encode on the device, copy the PNG bytes (not the float image) to the host, write `file`. */
 MCPT_API int mcpt_render_png(mcpt_ctx* ctx, const mcpt_camera* cam, int width, int height, int spp, int mode, int flags,
                              const char* file, mcpt_stats* stats);

@@ -80,6 +80,7 @@ SIGNATURES = {
                               C.POINTER(Stats)]),
     "mcpt_png_size": (C.c_int64, [C.c_int, C.c_int]),
     "mcpt_encode_png": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int64]),
+    "mcpt_encode_png_static": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p]),
     "mcpt_render_png": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p,
                                   C.POINTER(Stats)]),
     "mcpt_render_chunks": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -107,6 +108,7 @@ SIGNATURES = {
     "mcpt_render_scene_multi": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int]),
 }
 COMM_ID_BYTES = 128
+PNG_STATIC_BYTES = 8 << 20
 
 _lib = None
 

@@ -349,6 +349,15 @@ def write_png(file, rgb):
     check(lib().mcpt_write_png(file.encode(), a.ctypes.data_as(C.POINTER(C.c_float)), w, h))
 
 
+def encode_png_static(d_rgb_ptr, width, height, device=0, cuda_stream=0):
+    """mcpt_encode_png_static: device image -> PNG bytes without any allocation on the library's side (no Context needed); the
+    device scratch is a static 8 MiB array, so images beyond about 1920 x 1080 raise McptError."""
+    n = max(int(lib().mcpt_png_size(width, height)), 1)
+    out = np.empty(n, np.uint8)
+    check(lib().mcpt_encode_png_static(int(device), C.c_void_p(d_rgb_ptr), width, height, out.ctypes.data, n, C.c_void_p(cuda_stream)))
+    return out
+
+
 def png_size(width, height):
     """Size in bytes of the uncompressed PNG both the host and the device writer produce."""
     return int(lib().mcpt_png_size(width, height))

@@ -167,4 +167,61 @@ int launch_png_encode(const float* d_rgb, int w, int h, unsigned char* d_png, vo
     return (int)cudaGetLastError();
 }
 
-}  // namespace mcpt
+// ---- mcpt_encode_png_static: the output stage for callers that must not allocate ------------------------------------------
+// No counterpart in the reference.  mcpt_encode_png keeps its device-side PNG
+// buffer in a context and grows it with cudaMalloc; code under CUDA graph capture, tight serving loops and harnesses that forbid
+// allocation cannot call that.  This variant keeps the same scratch — 32 B of checksum accumulators (which must start at zero:
+// cleared by a cudaMemsetAsync on the caller's stream every call) and the encoded file before it is copied out — in ONE
+// file-scope device array of MCPT_PNG_STATIC_BYTES (8 MiB: up to 1920 x 1080; every GPU that loads libmcpt.so holds it until
+// exit).  It needs no mcpt_ctx and calls no cudaMalloc / cudaFree / allocating library routine.  Every call on a device shares
+// the array, which keeps the last call's contents: calls that overlap on the GPU (different streams, different threads) RACE.
+// In host code `g_png_static` is a host-side stand-in, not a device address: the address is asked of the runtime once per device,
+// with that device current (cudaGetSymbolAddress), and that pointer is what the kernels get.
+#define PNG_STATIC_HEADER 256   /* the accumulators; keeps the PNG bytes 256-B aligned */
+static __device__ __align__(256) unsigned char g_png_static[MCPT_PNG_STATIC_BYTES];
+
+}  // namespace mcpt (closed for the C entry point below)
+
+#include <mutex>
+#include <string>
+void mcpt_set_error(const char* msg);
+
+extern "C" MCPT_API int mcpt_encode_png_static(int device, const float* d_rgb, int width, int height, uint8_t* png_out, int64_t capacity,
+                                               void* cuda_stream) {
+    using namespace mcpt;
+    auto fail = [](int code, const std::string& m) { mcpt_set_error(m.c_str()); return code; };
+    if (!d_rgb || !png_out || width <= 0 || height <= 0) return fail(MCPT_ERR_ARG, "mcpt_encode_png_static: bad argument");
+    if (width > 21844) return fail(MCPT_ERR_ARG, "mcpt_encode_png_static: width > 21844 does not fit svpng's one-block-per-scanline framing");
+    const unsigned long long bytes = png_layout(width, height).total;
+    if (bytes + PNG_STATIC_HEADER > (unsigned long long)MCPT_PNG_STATIC_BYTES)
+        return fail(MCPT_ERR_ARG, "mcpt_encode_png_static: a " + std::to_string(width) + " x " + std::to_string(height) + " image encodes to " +
+                                      std::to_string(bytes) + " bytes, more than the static scratch holds (" +
+                                      std::to_string((unsigned long long)MCPT_PNG_STATIC_BYTES - PNG_STATIC_HEADER) +
+                                      " bytes, e.g. 1920 x 1080); use mcpt_encode_png");
+    if (capacity < (int64_t)bytes) return fail(MCPT_ERR_ARG, "mcpt_encode_png_static: output buffer smaller than mcpt_png_size()");
+    enum { MAX_DEV = 64 };
+    if (device < 0 || device >= MAX_DEV) return fail(MCPT_ERR_ARG, "mcpt_encode_png_static: device index out of range");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(MCPT_ERR_CUDA, std::string("mcpt_encode_png_static: cudaSetDevice: ") + cudaGetErrorName(e));
+    // set-up, once per device, with that device current: the DEVICE address of the array
+    static std::mutex mu;
+    static unsigned char* dev_ptr[MAX_DEV] = {};
+    unsigned char* base = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!dev_ptr[device]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_png_static);
+            if (e != cudaSuccess || !p) return fail(MCPT_ERR_CUDA, std::string("mcpt_encode_png_static: cudaGetSymbolAddress: ") + cudaGetErrorName(e));
+            dev_ptr[device] = (unsigned char*)p;
+        }
+        base = dev_ptr[device];
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const int le = launch_png_encode(d_rgb, width, height, base + PNG_STATIC_HEADER, base, st);   // clears the accumulators first
+    if (le) return fail(MCPT_ERR_CUDA, std::string("mcpt_encode_png_static: launch: ") + cudaGetErrorName((cudaError_t)le));
+    e = cudaMemcpyAsync(png_out, base + PNG_STATIC_HEADER, (size_t)bytes, cudaMemcpyDefault, st);   // png_out: host or device
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return fail(MCPT_ERR_CUDA, std::string("mcpt_encode_png_static: copy out: ") + cudaGetErrorName(e));
+    return MCPT_OK;
+}
