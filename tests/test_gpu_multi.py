@@ -47,8 +47,9 @@ def test_one_process_all_gpus_is_bit_identical(scenes, single, tmp_path):
             for mode in (M.MODE_WAVEFRONT, M.MODE_MEGAKERNEL):
                 img = m.render(s.camera, spp, w, h, mode=mode)
                 assert np.array_equal(img.view(np.uint32), base.view(np.uint32)), "%s R=%d mode %d differs" % (name, R, mode)
-                # every GPU traces its own primary rays (the cached primary hit lives in a path slot), so the ray total grows with R
-                assert m.last_stats.rays >= rays and m.last_stats.samples == w * h * spp and m.last_stats.exchange_ms > 0
+                # the ray total is not an invariant: every path slot / megakernel thread traces its own primary ray once (the cached
+                # primary hit lives in it), and their number depends on the GPU count and on the integrator
+                assert 0.5 * rays < m.last_stats.rays < 2.0 * rays and m.last_stats.samples == w * h * spp and m.last_stats.exchange_ms > 0
         # GPU-side ingest on every GPU + device PNG stage
         cam = m.load_scene_gpu(SCENES, "cornell-box"); m.build_bvh()
         w, h, spp, base, _ = single["cornell-box"]
