@@ -612,15 +612,16 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
     const int nch = ce - cb;
     const size_t plane = (size_t)width * height * 3;
     CU(grow(c->d_planes, c->planes_cap, sizeof(float) * plane * nch));
-    CU(grow(c->d_dirs, c->dirs_cap, sizeof(float) * plane));
+    const size_t dirs_bytes = (sizeof(float) * plane + 255) & ~(size_t)255;   // directions, then K7a's FP64 positions
+    CU(grow(c->d_dirs, c->dirs_cap, dirs_bytes + sizeof(double) * plane));
     c->wfh.iterations = 0;
     RenderParams P{};
     P.scene = device_scene(c);
     P.cam = make_camera(cam, width, height);
     P.cam_dirs = c->d_dirs;
-    const int er = launch_raygen(P.cam, c->d_dirs, c->stream);
-    if (er) return fail_cuda((cudaError_t)er, "raygen_kernel launch");
-    if (launches) *launches += 1;
+    const int er = launch_raygen(P.cam, c->d_dirs, (double*)((char*)c->d_dirs + dirs_bytes), c->stream);
+    if (er) return fail_cuda((cudaError_t)er, "raygen kernels launch");
+    if (launches) *launches += 2;
     P.spp = spp; P.chunk_begin = cb; P.n_chunks = nch;
     // enough threads to fill 148 SMs several times over, otherwise as many samples per thread as possible
     // Degree of parallelism = pixels x (chunks / chunks per thread).  Megakernel: enough threads to fill 148 SMs several

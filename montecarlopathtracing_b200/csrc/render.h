@@ -8,14 +8,14 @@ namespace mcpt {
 int launch_trace(const DeviceScene& sc, const float* d_org_dir, int n, mcpt_hit* d_hits, bool count,
                  unsigned long long* d_counters, cudaStream_t stream);
 // K7: primary ray directions (height*width*3 floats), bit-faithful to generateImg's repeated-addition pixel walk.
-int launch_raygen(const DCamera& cam, float* d_dirs, cudaStream_t stream);
+int launch_raygen(const DCamera& cam, float* d_dirs, double* d_pos, cudaStream_t stream);
 // K6: megakernel integrator; fills P.planes (P.n_chunks planes).
 int launch_megakernel(const RenderParams& P, int flags, cudaStream_t stream);
 // K8+K9: wavefront integrator (wavefront.cu); same planes as the megakernel, bit for bit.  The host reads the number of live path
 // slots one batch of iterations behind the GPU, so the stream never idles waiting for it.
 int wavefront_slots(const RenderParams& P);                    // < 0: too many slots for the 26-bit ray id
 size_t wavefront_scratch_bytes(int n_slots, int n_lights, long long n_pixels);
-enum { WF_MAX_PIPES = 4 };
+enum { WF_MAX_PIPES = 8 };
 struct WfHost {   // per-context host resources of the wavefront loop (created on first use)
     std::vector<cudaStream_t> side_streams;
     std::vector<cudaEvent_t> events;        // fork, join and per-pipe batch events

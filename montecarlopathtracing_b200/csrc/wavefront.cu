@@ -285,11 +285,12 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
 // from the queue head with one atomic for the warp.  Every loop iteration is one traversal step per lane: lanes at
 // an internal node take a node step; lanes at a leaf take a leaf step once `leaf_min` lanes have gathered there (or
 // no lane is at a node), so the triangle test is not issued for one or two lanes at a time.
-// Two parked leaves per lane instead of one: measured SLOWER (cornell-box 1465 -> 1396, veach-mis 680 -> 647 Msamples/s): lanes
-// at an internal node per issue rise only 13.6 -> 13.9, the extra bookkeeping costs more.  Kept as an A/B switch.
-#ifndef MCPT_PEND2
-#define MCPT_PEND2 0
-#endif
+// Two parked leaves per lane instead of one: measured SLOWER in round 1 (cornell-box 1465 -> 1396, veach-mis 680 -> 647 Msamples/s:
+// lanes at an internal node per issue rose only 13.6 -> 13.9, the bookkeeping in the node loop cost more).  What did pay (round 2):
+// the triangle phase always has TWO test slots (the second belongs to the second triangle of a two-triangle reference); a lane
+// whose parked reference holds one triangle and that already stands at its next leaf tests that leaf's first triangle in the free
+// slot, and a lane standing at a leaf after the phase parks it there and then, so it walks in the next node step instead of parking
+// (lanes per node-step issue on cornell-box 17.1 -> 19.4, node-step issues -12 %, 1 805 -> 1 870 Msamples/s).
 #ifndef MCPT_TRACE_MIN_CTAS
 #define MCPT_TRACE_MIN_CTAS 9
 #endif
@@ -342,9 +343,6 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
         }
     };
     int pend = 0;   // postponed leaf (negative ~k), 0 = none
-#if MCPT_PEND2
-    int pend2 = 0;  // a second one: leaves come in pairs (siblings), and a lane stuck at its second leaf walks no further
-#endif
     while (true) {
         const bool idle = node == MCPT_SENT && pend == 0;
         const unsigned im = __ballot_sync(0xffffffffu, idle);
@@ -393,9 +391,6 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
 #endif
             if (node < 0 && node != MCPT_SENT) {
                 if (pend == 0) { pend = node; node = stack.get(--sp); }
-#if MCPT_PEND2
-                else if (pend2 == 0) { pend2 = node; node = stack.get(--sp); }
-#endif
             }
         }
         const bool has_p = pend != 0;
@@ -409,12 +404,22 @@ __global__ void __launch_bounds__(128, MCPT_TRACE_MIN_CTAS) wf_trace(const Devic
         }
         if (COUNT && lane == 0) { w_iter++; if (pm != 0u && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) w_tri++; }
         if (has_p && (__popc(pm) >= leaf_min || __popc(bm) >= block_min || nm == 0u)) {
-            if (leaf_test<COUNT>(sc.tri, pend, r, best, n_tris, oc)) { node = MCPT_SENT; sp = 1; }   // shadow ray settled: occluded
-#if MCPT_PEND2
-            pend = pend2; pend2 = 0;
-#else
+            // Slot 1: the first triangle of the parked reference.  Slot 2: its second triangle; or, when it has none and the lane
+            // already stands at another leaf (it can walk no further until this phase), that leaf's first triangle — the lane keeps
+            // the rest of that reference, if any, as its node.
+            const int k = leaf_first(pend), dk = leaf_delta(pend);
+            bool settled = tri_test<COUNT>(sc.tri, k, r, best, n_tris, oc);
+            int k2 = dk ? k + dk : -1;
+            if (!dk && node < 0 && node != MCPT_SENT) {
+                k2 = leaf_first(node);
+                const int d2 = leaf_delta(node);
+                node = d2 ? ~(k2 + d2) : stack.get(--sp);
+            }
+            if (k2 >= 0) settled = tri_test<COUNT>(sc.tri, k2, r, best, n_tris, oc) || settled;
             pend = 0;
-#endif
+            if (settled) { node = MCPT_SENT; sp = 1; }   // shadow ray settled: occluded
+            // a lane that stands at a leaf parks it here rather than in the next iteration's first node step, which it then walks
+            else if (node < 0 && node != MCPT_SENT) { pend = node; node = stack.get(--sp); }
         }
     }
     if (has_ray) write_back();
@@ -465,7 +470,7 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
     if (n_slots <= 0 || nl > WF_MAX_LIGHTS) return (int)cudaErrorInvalidConfiguration;
     cudaError_t e;
 #define WF_CU(call) do { e = (call); if (e != cudaSuccess) return (int)e; } while (0)
-    int pipes = env_int("MCPT_WF_PIPES", 3);
+    int pipes = env_int("MCPT_WF_PIPES", 4);
     pipes = pipes < 1 ? 1 : pipes > WF_MAX_PIPES ? WF_MAX_PIPES : pipes;
     if (n_slots < 256 * 64 * pipes) pipes = 1;   // small images: one pipe already underfills the GPU
     while ((int)H.side_streams.size() < pipes - 1) { cudaStream_t s; WF_CU(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)); H.side_streams.push_back(s); }
@@ -512,7 +517,10 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
     const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE), mis = (flags & MCPT_FLAG_MIS_BALANCE) != 0;
     const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 12) / pipes;   // CTAs of 4 warps, shared by the pipes
     const int refill_min = env_int("MCPT_REFILL_MIN", 12), leaf_min = env_int("MCPT_LEAF_MIN", 1),
-              block_min = env_int("MCPT_BLOCK_MIN", 1), node_steps = env_int("MCPT_NODE_STEPS", MCPT_WIDE ? 2 : 4);
+              block_min = env_int("MCPT_BLOCK_MIN", 1),
+              // wide-node steps between two triangle phases: a ray of a large scene visits more nodes per leaf (5 M triangles: 10.5
+              // nodes and 4.0 triangle tests per ray, 3 steps +2.4 %; cornell-box: 6.3 and 4.2, 3 steps -0.6 %)
+              node_steps = env_int("MCPT_NODE_STEPS", MCPT_WIDE ? (P.scene.n_faces >= (1 << 20) ? 3 : 2) : 4);
     // A/B builds only (-DMCPT_SMEM_STACK=1 / -DMCPT_SMEM_TOP=K): dynamic shared memory of wf_trace = staged top nodes + a stack of
     // 1 + 3 * (levels of this scene's wide tree) entries per thread, thread-interleaved
     size_t trace_smem = 0;

@@ -35,7 +35,7 @@ def test_pixelwise_vs_oracle_same_random_numbers(gpu_ctx, oracle, scenes, name, 
     assert frac >= 0.99, "only %.4f of pixels match" % frac
     assert np.all(np.abs(img.mean(axis=(0, 1)) - ref.mean(axis=(0, 1))) <= 5e-3 * ref.mean(axis=(0, 1)))
     st = gpu_ctx.last_stats
-    assert st.samples == w * h * spp and st.kernel_launches == 3   # raygen + integrator + chunk sum
+    assert st.samples == w * h * spp and st.kernel_launches == 4   # raygen (walk + directions) + integrator + chunk sum
     # rays: one primary per pixel-thread group (reused, quirk Q4) + shadow rays with a positive receiver cosine + extends
     assert 0 < st.rays <= counts["primary"] + counts["shadow"] + counts["extend"]
 
