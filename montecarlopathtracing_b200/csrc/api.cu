@@ -641,7 +641,9 @@ int enqueue_chunks(mcpt_ctx* c, const mcpt_camera* cam, int width, int height, i
         // shortens the render's tail when a pixel has more than one slot to share them (3840 x 2160 and veach-mis had one)
         const char* v = getenv("MCPT_WF_MIN_GROUPS");
         int min_groups = v && *v ? atoi(v) : 4;   // measured 1 / 2 / 4: 3840x2160 3135 / 3277 / 3296 Msamples/s, veach-mis 712 / 729 / 733, 5 M triangles 946 / 945 / 967
-        while (g > 1 && nch / g < min_groups && (long long)width * height * (nch / (g >> 1)) <= (1LL << 25)) g >>= 1;
+        const char* m = getenv("MCPT_WF_MAX_SLOTS");
+        const long long max_slots = m && *m ? atoll(m) : (1LL << 25);
+        while (g > 1 && nch / g < min_groups && (long long)width * height * (nch / (g >> 1)) <= max_slots) g >>= 1;
     }
     P.chunks_per_thread = g;
     P.flags = flags;

@@ -31,7 +31,7 @@ enum { WFC_TAIL = 0, WFC_ALIVE = 2, WFC_HEAD = 4, WFC_COUNT = 8 };
 
 struct WfBuffers {
     float4* hit;     // last primary/extend result: (t, u, v, leaf as int bits)
-    float4* hit0;    // cached primary hit (quirk Q4: every sample of a pixel shares its primary ray)
+    float4* hit0;    // [pixel]: the pixel's primary hit (quirk Q4: every sample of a pixel shares its primary ray), written by wf_primary
     float4* sum_s;   // chunk sum rgb, next sample index (int bits)
     float4* beta_m;  // throughput rgb, meta bits (see META_*)
     float4* L;       // radiance of the sample in flight
@@ -77,6 +77,36 @@ __device__ __forceinline__ void push_ray(const bool pred, const WfBuffers& B, un
     }
 }
 
+// ---- K8a: one primary ray per PIXEL ----------------------------------------------------------------------------
+// Quirk Q4: all samples of a pixel share one un-jittered primary ray, so its hit is traced once, before the pipes fork, and every
+// slot of the pixel starts at the first vertex.  (Until round 2 every SLOT traced it — four times per pixel, 33 M rays at
+// 3840 x 2160 — and spent its first two iterations doing so.)  One thread per pixel, a warp per 8 x 4 tile: the rays of a warp are
+// as coherent as rays get, which is what the one-ray-per-thread traversal of seam 2 (trace_closest) is good at; it returns the
+// same hit as wf_trace, bit for bit (same node step, same triangle test, the closest-hit rule does not depend on visiting order).
+template <bool COUNT>
+__global__ void __launch_bounds__(128) wf_primary(const RenderParams P, float4* __restrict__ hit0) {
+    const int W = P.cam.width, H = P.cam.height;
+    const int tiles_x = (W + 7) >> 3, n_tiles = tiles_x * ((H + 3) >> 2);
+    const int tile = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    unsigned n_nodes = 0, n_tris = 0;
+    if (tile < n_tiles) {
+        const int tile_y = (int)fastdiv((unsigned)tile, P.div_tiles_x);
+        const int x = (tile - tile_y * tiles_x) * 8 + (lane & 7), y = tile_y * 4 + (lane >> 3);
+        if (x < W && y < H) {
+            const size_t pixel = (size_t)y * W + x;
+            const float3 o = f3((float)P.cam.eye[0], (float)P.cam.eye[1], (float)P.cam.eye[2]);
+            const float3 d = f3(__ldg(P.cam_dirs + 3 * pixel), __ldg(P.cam_dirs + 3 * pixel + 1), __ldg(P.cam_dirs + 3 * pixel + 2));
+            const Hit h = trace_closest<COUNT>(P.scene, o, d, 3.0e38f, n_nodes, n_tris);
+            hit0[pixel] = make_float4(h.t, h.u, h.v, __int_as_float(h.k));
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&P.counters[0], (unsigned long long)W * (unsigned long long)H);
+    if (COUNT) {
+        const unsigned a = __reduce_add_sync(0xffffffffu, n_nodes), b = __reduce_add_sync(0xffffffffu, n_tris);
+        if (lane == 0 && (a | b)) { atomicAdd(&P.counters[1], (unsigned long long)a); atomicAdd(&P.counters[2], (unsigned long long)b); }
+    }
+}
+
 // ---- K8: shade / path logic ------------------------------------------------------------------------------
 #ifndef MCPT_SHADE_MIN_CTAS
 #define MCPT_SHADE_MIN_CTAS 4
@@ -104,7 +134,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
     const bool jitter = (P.flags & MCPT_FLAG_JITTER) != 0, anyhit = (P.flags & MCPT_FLAG_ANYHIT_SHADOW) != 0;
 
     int state = WF_DONE, lobe = LOBE_DIFFUSE, chunk = 0, s = 0;
-    bool has_extend = false, have_hit0 = false, have_vertex = false, emit_primary = false, store_hit0 = false;
+    bool has_extend = false, have_hit0 = false, have_vertex = false, emit_primary = false;
     unsigned bounce = 0;
     float3 sum = f3(0.f, 0.f, 0.f), beta = f3(1.f, 1.f, 1.f), L = f3(0.f, 0.f, 0.f), rd = f3(0.f, 0.f, 0.f);
     float3 cam_d = f3(0.f, 0.f, 0.f), vdir = f3(0.f, 0.f, 0.f);
@@ -133,6 +163,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
 
     if (valid && !warp_was_done) {
         cam_d = f3(__ldg(P.cam_dirs + 3 * (size_t)pixel), __ldg(P.cam_dirs + 3 * (size_t)pixel + 1), __ldg(P.cam_dirs + 3 * (size_t)pixel + 2));
+        if (REUSE_PRIMARY) h0_in = __ldg(&B.hit0[pixel]);   // wf_primary's result: read-only for the whole loop
         if (iter == 0) {
             state = WF_NEW; chunk = P.chunk_begin + atomicAdd(&B.next_chunk[pixel], 1);
             s = (int)((long long)chunk * P.spp / MCPT_NUM_CHUNKS);
@@ -140,18 +171,18 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
             // all of the slot's state is requested at once (independent 16-B loads in flight) and decoded afterwards:
             // the kernel is latency-bound, not bandwidth-bound (ncu: 30 % issue, 21 % DRAM)
             const float4 bm = __ldcg(&B.beta_m[slot]);
-            ss_in = __ldcg(&B.sum_s[slot]); h0_in = __ldcg(&B.hit0[slot]); hit_in = __ldcg(&B.hit[slot]);
+            ss_in = __ldcg(&B.sum_s[slot]); hit_in = __ldcg(&B.hit[slot]);
             L_in = __ldcg(&B.L[slot]); rd_in = __ldcg(&B.rd[slot]); vis_in = __ldcg(&B.vis[slot]);
             const unsigned meta = __float_as_uint(bm.w);
-            state = meta & 3u; lobe = (meta >> 2) & 3u; has_extend = (meta >> 4) & 1u; have_hit0 = (meta >> 5) & 1u;
+            state = meta & 3u; lobe = (meta >> 2) & 3u; has_extend = (meta >> 4) & 1u;
             bounce = (meta >> 8) & 0xffu; chunk = (int)(meta >> 16);
             beta = f3(bm.x, bm.y, bm.z);
             was_done = state == WF_DONE;
             if (state != WF_DONE) {
                 sum = f3(ss_in.x, ss_in.y, ss_in.z); s = __float_as_int(ss_in.w);
-                if (have_hit0) { hit0.t = h0_in.x; hit0.u = h0_in.y; hit0.v = h0_in.z; hit0.k = __float_as_int(h0_in.w); }
             }
         }
+        if (REUSE_PRIMARY) { hit0.t = h0_in.x; hit0.u = h0_in.y; hit0.v = h0_in.z; hit0.k = __float_as_int(h0_in.w); have_hit0 = true; }
     }
     if (valid && state != WF_DONE) {
         int s_end = (int)((long long)(chunk + 1) * P.spp / MCPT_NUM_CHUNKS);
@@ -172,8 +203,7 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
         } else if (state == WF_WAIT_PRIMARY) {
             const float4 h4 = hit_in;
             Hit h; h.t = h4.x; h.u = h4.y; h.v = h4.z; h.k = __float_as_int(h4.w);
-            if (REUSE_PRIMARY) { hit0 = h; have_hit0 = true; store_hit0 = true; }
-            begin_path(h);
+            begin_path(h);   // only without primary-hit reuse (jitter, MCPT_FLAG_NO_PRIMARY_REUSE): every sample traces its own
         } else {   // WF_WAIT_VERTEX: resolve the vertex's NEE in light order, then look at the extend ray
             const float4 l4 = L_in;
             L = f3(l4.x, l4.y, l4.z);
@@ -263,7 +293,6 @@ __global__ void __launch_bounds__(256, MCPT_SHADE_MIN_CTAS) wf_shade(const Rende
                 __stcg(&B.L[slot], make_float4(L.x, L.y, L.z, 0.f));
                 if (has_extend) __stcg(&B.rd[slot], make_float4(rd.x, rd.y, rd.z, pdf_b));
             }
-            if (store_hit0) __stcg(&B.hit0[slot], make_float4(hit0.t, hit0.u, hit0.v, __int_as_float(hit0.k)));
         }
     } else if (slot < B.slot_end && iter == 0) {
         __stcg(&B.beta_m[slot], make_float4(0.f, 0.f, 0.f, __uint_as_float(pack_meta(WF_DONE, 0, false, false, 0, 0))));
@@ -446,7 +475,7 @@ int wavefront_slots(const RenderParams& P) {
 
 size_t wavefront_scratch_bytes(int n_slots, int n_lights, long long n_pixels) {
     const size_t n = (size_t)n_slots;
-    return 6 * align256(16 * n) + align256(16 * n * (size_t)(n_lights > 0 ? n_lights : 1)) + align256(4 * n) + align256(n / 32 + 1) + align256(4 * (size_t)n_pixels) +
+    return 5 * align256(16 * n) + align256(16 * (size_t)n_pixels) + align256(16 * n * (size_t)(n_lights > 0 ? n_lights : 1)) + align256(4 * n) + align256(n / 32 + 1) + align256(4 * (size_t)n_pixels) +
            2 * align256(16 * n * (size_t)(n_lights + 1)) + align256(4 * WFC_COUNT * WF_MAX_PIPES);
 }
 
@@ -481,12 +510,12 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
     char* p = (char*)scratch;
     auto take = [&](size_t bytes) { char* r = p; p += align256(bytes); return r; };
     const size_t n = (size_t)n_slots;
-    B0.hit = (float4*)take(16 * n); B0.hit0 = (float4*)take(16 * n); B0.sum_s = (float4*)take(16 * n);
+    const size_t n_pixels = (size_t)P.cam.width * P.cam.height;
+    B0.hit = (float4*)take(16 * n); B0.hit0 = (float4*)take(16 * n_pixels); B0.sum_s = (float4*)take(16 * n);
     B0.beta_m = (float4*)take(16 * n); B0.L = (float4*)take(16 * n); B0.rd = (float4*)take(16 * n);
     B0.pend = (float4*)take(16 * n * (size_t)(nl > 0 ? nl : 1));
     B0.vis = (unsigned*)take(4 * n);
     B0.warp_done = (unsigned char*)take(n / 32 + 1);
-    const size_t n_pixels = (size_t)P.cam.width * P.cam.height;
     B0.next_chunk = (int*)take(4 * n_pixels);
     WF_CU(cudaMemsetAsync(B0.next_chunk, 0, 4 * n_pixels, stream));
     B0.ray_o = (float4*)take(16 * n * (size_t)(nl + 1)); B0.ray_d = (float4*)take(16 * n * (size_t)(nl + 1));
@@ -509,12 +538,19 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
         q.shade_blocks = (q.B.slot_end - q.B.slot_begin + 255) / 256;
         q.done = q.shade_blocks == 0;
     }
-    // fork: the side streams start after everything already enqueued on `stream` (raygen, counter reset)
+    const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE), mis = (flags & MCPT_FLAG_MIS_BALANCE) != 0;
+    int nlaunch = 0;
+    if (reuse) {   // the pixels' shared primary hits, once, before the pipes fork
+        const unsigned tiles = (unsigned)(((P.cam.width + 7) >> 3) * ((P.cam.height + 3) >> 2));
+        if (count) wf_primary<true><<<(tiles + 3) / 4, 128, 0, stream>>>(P, B0.hit0);
+        else wf_primary<false><<<(tiles + 3) / 4, 128, 0, stream>>>(P, B0.hit0);
+        nlaunch++;
+    }
+    // fork: the side streams start after everything already enqueued on `stream` (raygen, counter reset, primary hits)
     cudaEvent_t ev_fork = H.events[0];
     WF_CU(cudaEventRecord(ev_fork, stream));
     for (int k = 1; k < pipes; k++) WF_CU(cudaStreamWaitEvent(pp[k].st, ev_fork, 0));
 
-    const bool count = flags & MCPT_FLAG_COUNT, reuse = !(flags & MCPT_FLAG_NO_PRIMARY_REUSE), mis = (flags & MCPT_FLAG_MIS_BALANCE) != 0;
     const int trace_blocks = 148 * env_int("MCPT_TRACE_CTAS_PER_SM", 12) / pipes;   // CTAs of 4 warps, shared by the pipes
     const int refill_min = env_int("MCPT_REFILL_MIN", 12), leaf_min = env_int("MCPT_LEAF_MIN", 1),
               block_min = env_int("MCPT_BLOCK_MIN", 1),
@@ -531,7 +567,7 @@ int launch_wavefront(const RenderParams& P, int flags, void* scratch, WfHost& H,
 #endif
     const int batch = 8;
     const bool diag = getenv("MCPT_DIAG_ALIVE") != nullptr;
-    int nlaunch = 0, n_timed = 0;
+    int n_timed = 0;
     for (int b = 0;; b++) {
         bool any = false;
         for (int k = 0; k < pipes; k++) {

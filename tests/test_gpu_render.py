@@ -210,7 +210,8 @@ def test_synthetic_scene_with_glass(gpu_ctx, oracle):
 @pytest.mark.parametrize("name,w,h,spp", [("cornell-box", 200, 120, 24), ("veach-mis", 160, 120, 12), ("cornell-box", 61, 35, 5)])
 def test_wavefront_equals_megakernel_bit_for_bit(gpu_ctx, scenes, name, w, h, spp):
     """Both integrators key Philox by (pixel, sample), call the same per-vertex arithmetic (shade.cuh) and add samples
-    in sample order, so their images must be IDENTICAL, and so must their ray counts."""
+    in sample order, so their images must be IDENTICAL.  Ray counts: the same shadow and extend rays; the wavefront path traces
+    ONE primary ray per pixel (wf_primary), the megakernel one per thread that has samples."""
     s = scenes[name]
     _load(gpu_ctx, s)
     gpu_ctx.set_seed(11)
@@ -219,7 +220,7 @@ def test_wavefront_equals_megakernel_bit_for_bit(gpu_ctx, scenes, name, w, h, sp
     b = gpu_ctx.render(s.camera, spp, w, h, mode=M.MODE_WAVEFRONT)
     st = gpu_ctx.last_stats
     assert np.array_equal(a, b), "max abs diff %g" % np.abs(a - b).max()
-    assert st.rays == rays_a and st.samples == w * h * spp and st.kernel_launches > 3
+    assert w * h < st.rays <= rays_a and st.samples == w * h * spp and st.kernel_launches > 3
     c = gpu_ctx.render(s.camera, spp, w, h, mode=M.MODE_WAVEFRONT, flags=M.FLAG_NO_PRIMARY_REUSE | M.FLAG_COUNT)
     assert np.array_equal(a, c) and gpu_ctx.last_stats.node_visits > 0
     nodes_early = gpu_ctx.last_stats.node_visits
