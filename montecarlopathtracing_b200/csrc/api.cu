@@ -106,7 +106,7 @@ int alloc_scene(mcpt_ctx* c, int n) {
         carve(s.codes_obj, N); carve(s.codes_sorted, N); carve(s.iota, N); carve(s.leaf_face, N);
         carve(s.leaf_parent, N); carve(s.flags, N); carve(s.nodes, N); carve(s.tri, N);
         carve(s.shade, N); carve(s.root_box, 6); carve(s.qnodes, N); carve(s.qgrid, 1);
-        carve(s.qnodes4, N); carve(s.w4_queue, N); carve(s.w4_ctr, 8);
+        carve(s.qnodes4, N); carve(s.w4_queue, N); carve(s.w4_ctr, 16); carve(s.w4_cand, n - 1 <= W4_SMALL_MAX_N ? N : 1);
         carve(s.nodes2, N); carve(s.cl_lo[0], N); carve(s.cl_lo[1], N); carve(s.cl_hi[0], N); carve(s.cl_hi[1], N);
         carve(s.ploc_flag, N);
         carve_bytes(s.ploc_temp, s.ploc_temp_bytes); carve_bytes(s.ploc_state, 64); carve_bytes(s.cub_temp, s.cub_temp_bytes);

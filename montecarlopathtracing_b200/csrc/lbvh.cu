@@ -242,7 +242,7 @@ int lbvh_build(SceneBuffers& sb, cudaStream_t stream, const BuildStreams& bs, in
     const int n = sb.n_faces;
     const int tpb = 256;
     int nl = 0;
-    cudaError_t e = cudaMemsetAsync(sb.w4_ctr, 0, 8 * sizeof(unsigned), stream);   // [5] = K1's bad-vertex flag
+    cudaError_t e = cudaMemsetAsync(sb.w4_ctr, 0, 16 * sizeof(unsigned), stream);   // [5] = K1's bad-vertex flag
     if (e != cudaSuccess) return (int)e;
     morton_kernel<<<(n + tpb - 1) / tpb, tpb, 0, stream>>>(sb.pos, n, sb.codes_obj, sb.iota, sb.flags, sb.w4_ctr + 5); nl++;
     // stable LSD radix sort of (code, face index), 30 key bits: ties keep face-index order

@@ -4,6 +4,8 @@
 
 namespace mcpt {
 
+#define W4_SMALL_MAX_N 65536   /* up to this many binary nodes the wide collapse runs as candidates + one cluster (wide.cu) */
+
 struct SceneBuffers {
     int n_faces = 0;
     // uploaded inputs, OBJ order (mcpt_scene_desc)
@@ -23,7 +25,8 @@ struct SceneBuffers {
     QGrid* qgrid = nullptr;
     QNode4* qnodes4 = nullptr;         // 4-wide traversal nodes (wide.cu), breadth-first, root = 0
     int* w4_queue = nullptr;           // wide node -> the binary node it is rooted at
-    unsigned* w4_ctr = nullptr;        // queue tail (= number of wide nodes), processed, finished, error, internal levels
+    QNode4* w4_cand = nullptr;         // small scenes (<= W4_SMALL_MAX_N nodes): every binary node as the root of a wide node (wide.cu)
+    unsigned* w4_ctr = nullptr;        // 16 words: queue tail (= number of wide nodes), processed, finished, error, internal levels, K1's bad-vertex flag, -, -, three per-level counters
     int w4_resident_blocks = 0;        // co-resident CTAs of wide_collapse_kernel on this context's device (occupancy query)
     unsigned* build_err = nullptr;     // device flag set by K1 when a vertex is not finite or beyond +-1e18 (checked by mcpt_build_bvh)
     void* cub_temp = nullptr; size_t cub_temp_bytes = 0;

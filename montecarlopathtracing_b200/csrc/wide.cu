@@ -139,84 +139,108 @@ __global__ void __launch_bounds__(256) wide_collapse_kernel(const BvhNode* __res
 }
 
 
-// ---- small trees: ONE thread-block cluster, level by level ---------------------------------------------------------------
+// ---- small trees: candidates for every binary node at once, then ONE thread-block cluster, level by level ---------------------
 // Below ~64 Ki triangles the kernel above is nothing but a latency chain: a level's nodes are found by POLLING the queue through
-// L2, one level after the other (cornell-box: 118 us for 6 300 wide nodes in ~10 levels).  Here the 8 CTAs of one cluster take a
-// whole level at a time — its entries are the queue slots [begin, end) — and meet at the hardware cluster barrier (two per
-// level: one so that every CTA sees the level's queue entries and tail, one so that nobody moves the tail before all have read
-// it).  Same collapse rule, same tree; sibling numbering again depends on the order of the atomics only.
+// L2, one level after the other (cornell-box: 118 us for 6 300 wide nodes in ~10 levels).  Two steps instead:
+//   wide_candidates_kernel   what EVERY binary node would look like as the root of a wide node — its (up to) four children by the
+//                            opening rule above, boxes already on the 16-bit grid, references still binary ids.  No node depends
+//                            on another, so the ~8 dependent L2 round trips of the rule (node, children, folded grandchildren,
+//                            twice more) are paid ONCE, by all nodes in parallel, instead of once per level.
+//   wide_collapse_small_kernel  the 8 CTAs of one cluster take a whole level at a time — its entries are the queue slots
+//                            [begin, end) — read each entry's candidate (one 64-B fetch), number its internal children with one
+//                            atomic per warp and meet at the hardware cluster barrier, ONE per level: level L counts its new
+//                            entries in counter L mod 3, which is read after the barrier and cleared again during level L + 1.
+// Same collapse rule, same tree as the polling kernel; sibling numbering again depends on the order of the atomics only.
+// cornell-box: 94 us (one kernel, two barriers and ~8 round trips per level) -> 8 + 35 us; veach-mis' build 0.23 -> 0.17 ms.
 #define W4_SMALL_CTAS 8
 #define W4_SMALL_TPB 512
-#define W4_SMALL_MAX_N 65536
-__global__ void __launch_bounds__(W4_SMALL_TPB) wide_collapse_small_kernel(const BvhNode* __restrict__ nodes, const int root2, const int max_nodes,
-                                                                           const float* __restrict__ root_box, QNode4* __restrict__ out,
-                                                                           int* queue, unsigned* ctr, const bool fold, QGrid* __restrict__ qgrid) {
-    cg::cluster_group cluster = cg::this_cluster();
-    const int nthreads = W4_SMALL_CTAS * W4_SMALL_TPB, gtid = blockIdx.x * W4_SMALL_TPB + threadIdx.x, lane = threadIdx.x & 31;
+enum { W4_LEVEL_CTR = 8 };   // ctr[8..10]: the rotating per-level counters (zero outside the kernel)
+
+__global__ void __launch_bounds__(256) wide_candidates_kernel(const BvhNode* __restrict__ nodes, const int n_nodes, const float* __restrict__ root_box,
+                                                              QNode4* __restrict__ cand, const bool fold, QGrid* __restrict__ qgrid) {
+    const int id = blockIdx.x * blockDim.x + threadIdx.x;
     float o[3], cell[3], inv[3];
     quant_grid(root_box, o, cell, inv);
-    if (gtid == 0) {
+    if (id == 0) {
         qgrid->origin = make_float4(o[0], o[1], o[2], 0.0f);
         qgrid->cell = make_float4(cell[0], cell[1], cell[2], 0.0f);
     }
+    if (id >= n_nodes) return;
+    W4Slot s[4];
+    int cnt = 2;
+    w4_children(nodes, id, fold, s[0], s[1]);
+    for (int step = 0; step < 2; step++) {
+        int pick = -1; float best = -1.0f;
+        for (int j = 0; j < cnt; j++) {
+            const float a = w4_area(s[j]);
+            if (s[j].ref >= 0 && a > best) { best = a; pick = j; }
+        }
+        if (pick < 0) break;
+        const int open = s[pick].ref;
+        w4_children(nodes, open, fold, s[pick], s[cnt]);
+        cnt++;
+    }
+    QNode4 q;
+    for (int j = 0; j < 4; j++) {
+        if (j < cnt) {
+            q.c[j] = make_uint4(quant_lo(s[j].lo[0], o[0], inv[0]) | (quant_hi(s[j].hi[0], o[0], inv[0]) << 16),
+                                quant_lo(s[j].lo[1], o[1], inv[1]) | (quant_hi(s[j].hi[1], o[1], inv[1]) << 16),
+                                quant_lo(s[j].lo[2], o[2], inv[2]) | (quant_hi(s[j].hi[2], o[2], inv[2]) << 16), (unsigned)s[j].ref);
+        } else {
+            q.c[j] = make_uint4(0x0000FFFFu, 0x0000FFFFu, 0x0000FFFFu, 0x80000000u);   // inverted box: never hit
+        }
+    }
+    cand[id] = q;
+}
+
+__global__ void __launch_bounds__(W4_SMALL_TPB) wide_collapse_small_kernel(const QNode4* __restrict__ cand, const int root2, const int max_nodes,
+                                                                           QNode4* __restrict__ out, int* queue, unsigned* ctr) {
+    cg::cluster_group cluster = cg::this_cluster();
+    const int nthreads = W4_SMALL_CTAS * W4_SMALL_TPB, gtid = blockIdx.x * W4_SMALL_TPB + threadIdx.x, lane = threadIdx.x & 31;
     int begin = 0, end = 1;
     unsigned levels = 0;
-    __shared__ int s_end;
+    __shared__ unsigned s_new;
     while (begin < end && end <= max_nodes) {
+        unsigned* level_ctr = ctr + W4_LEVEL_CTR + levels % 3u;
         for (int base = begin + (gtid - lane); base < end; base += nthreads) {   // warp-uniform trip count
             const int t = base + lane;
             const bool active = t < end;
-            W4Slot s[4];
-            int cnt = 0, m = 0;
+            uint4 c0 = make_uint4(0u, 0u, 0u, 0x80000000u), c1 = c0, c2 = c0, c3 = c0;
+            int m = 0;
             if (active) {
                 const int id = t == 0 ? root2 : __ldcg(&queue[t]);
-                cnt = 2;
-                w4_children(nodes, id, fold, s[0], s[1]);
-                for (int step = 0; step < 2; step++) {
-                    int pick = -1; float best = -1.0f;
-                    for (int j = 0; j < cnt; j++) {
-                        const float a = w4_area(s[j]);
-                        if (s[j].ref >= 0 && a > best) { best = a; pick = j; }
-                    }
-                    if (pick < 0) break;
-                    const int open = s[pick].ref;
-                    w4_children(nodes, open, fold, s[pick], s[cnt]);
-                    cnt++;
-                }
-                for (int j = 0; j < cnt; j++) m += s[j].ref >= 0;
+                c0 = cand[id].c[0]; c1 = cand[id].c[1]; c2 = cand[id].c[2]; c3 = cand[id].c[3];
+                m = ((int)c0.w >= 0) + ((int)c1.w >= 0) + ((int)c2.w >= 0) + ((int)c3.w >= 0);
             }
             int incl = m;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
             const int total = __shfl_sync(0xffffffffu, incl, 31);
             unsigned at = 0;
-            if (lane == 0 && total) at = atomicAdd(&ctr[W4_TAIL], (unsigned)total);
-            at = __shfl_sync(0xffffffffu, at, 0) + (unsigned)(incl - m);
+            if (lane == 0 && total) at = atomicAdd(level_ctr, (unsigned)total);
+            at = (unsigned)end + __shfl_sync(0xffffffffu, at, 0) + (unsigned)(incl - m);
             if (active) {
-                QNode4 q;
-                int k = 0;
-                for (int j = 0; j < 4; j++) {
-                    if (j < cnt) {
-                        int ref = s[j].ref;
-                        if (ref >= 0) { const int w = (int)at + k++; __stcg(&queue[w], ref); ref = w; }
-                        q.c[j] = make_uint4(quant_lo(s[j].lo[0], o[0], inv[0]) | (quant_hi(s[j].hi[0], o[0], inv[0]) << 16),
-                                            quant_lo(s[j].lo[1], o[1], inv[1]) | (quant_hi(s[j].hi[1], o[1], inv[1]) << 16),
-                                            quant_lo(s[j].lo[2], o[2], inv[2]) | (quant_hi(s[j].hi[2], o[2], inv[2]) << 16), (unsigned)ref);
-                    } else {
-                        q.c[j] = make_uint4(0x0000FFFFu, 0x0000FFFFu, 0x0000FFFFu, 0x80000000u);   // inverted box: never hit
-                    }
+                if (at + (unsigned)m <= (unsigned)max_nodes) {   // (a tree can never need more: the test only guards the queue)
+                    if ((int)c0.w >= 0) { __stcg(&queue[at], (int)c0.w); c0.w = at++; }
+                    if ((int)c1.w >= 0) { __stcg(&queue[at], (int)c1.w); c1.w = at++; }
+                    if ((int)c2.w >= 0) { __stcg(&queue[at], (int)c2.w); c2.w = at++; }
+                    if ((int)c3.w >= 0) { __stcg(&queue[at], (int)c3.w); c3.w = at++; }
                 }
-                out[t] = q;
+                out[t].c[0] = c0; out[t].c[1] = c1; out[t].c[2] = c2; out[t].c[3] = c3;
             }
         }
-        levels++;
-        cluster.sync();                                   // the level's queue entries and tail reservations are complete
-        if (threadIdx.x == 0) s_end = (int)__ldcg(&ctr[W4_TAIL]);
+        cluster.sync();                                   // the level's queue entries and its count are complete
+        if (threadIdx.x == 0) s_new = __ldcg(level_ctr);
+        if (gtid == 0) ctr[W4_LEVEL_CTR + (levels + 2u) % 3u] = 0u;   // last read before this barrier, next used after the next one
         __syncthreads();
-        begin = end; end = s_end;
-        cluster.sync();                                   // everybody has read the tail before the next level moves it
+        begin = end; end += (int)s_new;                   // (s_new is rewritten only after the next cluster barrier)
+        levels++;
     }
-    if (gtid == 0) { ctr[W4_PROCESSED] = (unsigned)end; ctr[W4_LEVELS] = levels; ctr[W4_ERROR] = end > max_nodes ? 1u : 0u; ctr[W4_FINISHED] = 1u; }
+    cluster.sync();
+    if (gtid == 0) {
+        ctr[W4_LEVEL_CTR] = 0u; ctr[W4_LEVEL_CTR + 1] = 0u; ctr[W4_LEVEL_CTR + 2] = 0u;
+        ctr[W4_TAIL] = (unsigned)end; ctr[W4_PROCESSED] = (unsigned)end; ctr[W4_LEVELS] = levels; ctr[W4_ERROR] = end > max_nodes ? 1u : 0u; ctr[W4_FINISHED] = 1u;
+    }
 }
 
 int wide_build(SceneBuffers& sb, const BvhNode* walk, int root2, cudaStream_t stream, int* launches, bool prepared) {
@@ -229,22 +253,24 @@ int wide_build(SceneBuffers& sb, const BvhNode* walk, int root2, cudaStream_t st
         wide_init_kernel<<<1, 1, 0, stream>>>(sb.w4_ctr);
         if (launches) *launches += 2;
     }
-    if (max_nodes <= W4_SMALL_MAX_N) {   // one cluster, level by level
+    if (max_nodes <= W4_SMALL_MAX_N) {   // small trees: candidates for every binary node, then one cluster, level by level
+        const bool fold_s = sb.fold_pairs && n > 2;
+        wide_candidates_kernel<<<(max_nodes + 255) / 256, 256, 0, stream>>>(walk, max_nodes, (const float*)sb.root_box, sb.w4_cand, fold_s, sb.qgrid);
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(W4_SMALL_CTAS); cfg.blockDim = dim3(W4_SMALL_TPB); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = W4_SMALL_CTAS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr; cfg.numAttrs = 1;
-        const bool fold_s = sb.fold_pairs && n > 2;
-        e = cudaLaunchKernelEx(&cfg, wide_collapse_small_kernel, walk, root2, max_nodes, (const float*)sb.root_box, sb.qnodes4, sb.w4_queue,
-                               sb.w4_ctr, fold_s, sb.qgrid);
-        if (launches) *launches += 1;
+        e = cudaLaunchKernelEx(&cfg, wide_collapse_small_kernel, (const QNode4*)sb.w4_cand, root2, max_nodes, sb.qnodes4, sb.w4_queue, sb.w4_ctr);
+        if (launches) *launches += 2;
         return (int)(e != cudaSuccess ? e : cudaGetLastError());
     }
-    // a fully RESIDENT grid (the no-deadlock argument needs every thread to be running): launched COOPERATIVELY, so the runtime
-    // refuses the launch instead of letting CTAs wait for SMs that another context or stream holds; the grid size comes from
-    // this device's occupancy (queried once per context: sb.w4_resident_blocks)
+    // large trees: a fully RESIDENT grid polling the queue (the no-deadlock argument needs every thread to be running): launched
+    // COOPERATIVELY, so the runtime refuses the launch instead of letting CTAs wait for SMs that another context or stream holds;
+    // the grid size comes from this device's occupancy (queried once per context: sb.w4_resident_blocks).  The opening rule is
+    // evaluated on demand here: candidates for all n - 1 binary nodes (3.6 x the nodes that end up in the tree) cost more than the
+    // shorter polling chain saves (measured: 1 M triangles 0.98 -> 0.94 ms, 5 M 2.73 -> 2.77 ms; the large case decides).
     if (!sb.w4_resident_blocks) {
         int dev = 0, sms = 0, per_sm = 0, coop = 0;
         cudaGetDevice(&dev);
