@@ -218,7 +218,9 @@ __global__ void __launch_bounds__(256) quantize_nodes_kernel(int n_nodes, const 
 // ---- sort ------------------------------------------------------------------------------------------------------------
 // cub::DeviceRadixSort::SortPairs over 30 key bits (a single-tile kernel below ~4.8 k keys, histogram + scan + four onesweep
 // passes above): LSD, hence stable — ties keep face order, the canonical leaf order.  Measured and dropped: one CTA of 1024
-// threads x 16 keys with cub::BlockRadixSort for up to 16 Ki keys (70.8 us for cornell-box's 15 056 keys against 62 us here).
+// threads x 16 keys with cub::BlockRadixSort for up to 16 Ki keys (70.8 us for cornell-box's 15 056 keys against 62 us here); an
+// all-pairs rank sort for n <= 16 Ki (rank = #{j : code_j < code_i + (j < i)}, segments in shared memory, two launches): correct,
+// 51 + 4 us against 57 us — 2.3e8 compare-and-count pairs are ~3 half-rate ALU instructions each.
 static int sort_codes(SceneBuffers& sb, cudaStream_t stream, int* nl) {
     const int n = sb.n_faces;
     cudaError_t e = cub::DeviceRadixSort::SortPairs(sb.cub_temp, sb.cub_temp_bytes, sb.codes_obj, sb.codes_sorted, sb.iota,
