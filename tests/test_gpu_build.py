@@ -239,7 +239,9 @@ def test_wide_tree_invariants_on_shipped_scenes(gpu_ctx, scenes, name):
     assert leaf_sets(nodes) == leaf_sets(nodes2)
 
 
-@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 7, 64, 1001, 1025, 5000])
+# 40 000: levels wider than the 4 096 threads of the small-tree cluster (several trips per level); 65 537 / 65 538: the last size on
+# the cluster path (candidates + level pass) and the first on the polling kernel
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 7, 64, 1001, 1025, 5000, 40000, 65537, 65538])
 def test_wide_tree_small_counts(gpu_ctx, n):
     desc, keep = random_soup(n, seed=n, far_outside=(n == 64))
     gpu_ctx.upload_scene(desc)
