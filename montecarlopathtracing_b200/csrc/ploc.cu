@@ -13,6 +13,8 @@
 // The rounds above 1024 clusters run in ONE cooperatively launched persistent kernel (two grid barriers per round), then a
 // single CTA finishes the job in shared memory.  Node boxes are exact unions of the
 // padded FP32 leaf boxes of K3, so no refit is needed.  Leaf order, leaf indices and the Morton codes are untouched.
+#include <cstdio>
+#include <cstdlib>
 #include <cooperative_groups.h>
 #include <cub/block/block_scan.cuh>
 #include "lbvh.h"
@@ -27,7 +29,7 @@ namespace mcpt {
 #define PLOC_GRID_TPB 256      /* cooperative-grid variant of the rounds kernel */
 #define PLOC_CLUSTER_TPB 1024  /* one-cluster variant */
 #define PLOC_CLUSTER_CTAS 8
-#define PLOC_CLUSTER_MAX_N 0   /* measured: cornell-box 125 us in one cluster (8 SMs do all the work) against 91 us on the cooperative grid (59 SMs): parallelism beats barrier latency; the variant stays for A/B */
+#define PLOC_CLUSTER_MAX_N 0   /* measured: cornell-box 125 us in one cluster (8 SMs do all the work) against 91 us on the cooperative grid (59 SMs): parallelism beats barrier latency; the variant stays for A/B.  Also measured: the grid down to 4096 clusters, then one cluster of 8 x 256 threads down to 1024: 38 + 62 us against 84 us — two tiles per CTA and round with 8 warps per SM hide no latency */
 #define PLOC_FINISH 1024
 #define PLOC_MAX_ITERS 4096
 
@@ -79,7 +81,7 @@ __device__ __forceinline__ void write_node(BvhNode* nodes, int id, const float4 
 //            in every CTA, no global state), scans its flags tile by tile and scatters survivors / writes the new nodes
 //            in array order — so node numbering does not depend on scheduling                          -> grid.sync
 #define PLOC_HALO (2 * PLOC_RADIUS)
-struct PlocState { int m; int node_base; int error; int rounds; };   // clusters alive, internal nodes created, stalled, rounds run
+struct PlocState { int m; int node_base; int error; int rounds; int finish_rounds; };   // clusters alive, internal nodes created, stalled, rounds run (grid kernel | buffer parity << 30), rounds of the finish kernel
 
 // CLUSTER: the CTAs are ONE thread-block cluster (8 CTAs of 1024 threads) and the barrier is the hardware cluster barrier — a
 // fraction of a microsecond against ~3 us for a grid-wide barrier through L2; used up to 64 Ki triangles, where a round is
@@ -208,7 +210,7 @@ __global__ void __launch_bounds__(PLOC_FINISH) ploc_finish_kernel(PlocState* st,
                                                                   BvhNode* __restrict__ nodes, float* __restrict__ root_box, unsigned* w4_ctr) {
     __shared__ float4 slo[PLOC_FINISH + 2 * PLOC_RADIUS], shi[PLOC_FINISH + 2 * PLOC_RADIUS];   // clusters at [RADIUS, RADIUS + m)
     __shared__ int snn[PLOC_FINISH];
-    __shared__ unsigned s_cnt[2][32];
+    __shared__ unsigned s_cnt[1][32];
     const int i = threadIdx.x, lane = i & 31, warp = i >> 5;
     const unsigned lt_mask = (1u << lane) - 1u;
     if (i == 0 && w4_ctr) { w4_ctr[0] = 1u; w4_ctr[1] = 0u; w4_ctr[2] = 0u; w4_ctr[3] = 0u; w4_ctr[4] = 0u; }   // wide.cu's W4_* counters
@@ -219,7 +221,15 @@ __global__ void __launch_bounds__(PLOC_FINISH) ploc_finish_kernel(PlocState* st,
     if (i < m) { slo[i + PLOC_RADIUS] = lo[i]; shi[i + PLOC_RADIUS] = hi[i]; }
     __syncthreads();
     int rounds = 0;
+    // Only the warps that still hold clusters take part in a round: a warp whose first thread is beyond the cluster count leaves
+    // for good (the count only shrinks) and the others meet at a NAMED barrier sized for them — with all 32 warps at every barrier
+    // and every warp repeating the bookkeeping, two thirds of the kernel's 177 k warp instructions were issued by warps with
+    // nothing to cluster, and `barrier` was its top stall (13 warps per issue).
     while (m > 1) {
+        const int n_act = (m + 31) >> 5;                      // warps with clusters this round; the same value in every thread
+        if (warp >= n_act) return;
+        const int bar_threads = n_act * 32;
+        auto act_sync = [&] { asm volatile("bar.sync 1, %0;" :: "r"(bar_threads) : "memory"); };
         float4 alo = make_float4(0.f, 0.f, 0.f, 0.f), ahi = alo;
         int bj = -1;
         if (i < m) {
@@ -227,7 +237,7 @@ __global__ void __launch_bounds__(PLOC_FINISH) ploc_finish_kernel(PlocState* st,
             bj = ploc_nearest(slo, shi, i + PLOC_RADIUS, i, m);
             snn[i] = bj;
         }
-        __syncthreads();
+        act_sync();
         bool survive = false, left = false;
         float4 blo = alo, bhi = ahi;
         if (i < m) {
@@ -235,20 +245,16 @@ __global__ void __launch_bounds__(PLOC_FINISH) ploc_finish_kernel(PlocState* st,
             survive = !(mutual && i > bj); left = mutual && i < bj;
             if (left) { blo = slo[bj + PLOC_RADIUS]; bhi = shi[bj + PLOC_RADIUS]; }
         }
-        // order-preserving compaction with warp ballots + one 32-wide shuffle scan of the per-warp counts (every warp does the
-        // same scan, so the totals need no broadcast): three barriers per round where a 1024-thread cub::BlockScan took six
+        // order-preserving compaction with warp ballots; the per-warp counts (survivors | merges << 16, both <= 1024) are summed by
+        // every active warp with two REDUX instructions — all counts, and the counts of the warps before it — so the totals need no
+        // broadcast: three barriers per round where a 1024-thread cub::BlockScan took six
         const unsigned ms = __ballot_sync(0xffffffffu, survive), ml = __ballot_sync(0xffffffffu, left);
-        if (lane == 0) { s_cnt[0][warp] = (unsigned)__popc(ms); s_cnt[1][warp] = (unsigned)__popc(ml); }
-        __syncthreads();   // everyone has read slo/shi/snn; the counts are in
-        unsigned cs = s_cnt[0][lane], cl = s_cnt[1][lane];
-        unsigned is = cs, il = cl;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned vs = __shfl_up_sync(0xffffffffu, is, d), vl = __shfl_up_sync(0xffffffffu, il, d);
-            if (lane >= d) { is += vs; il += vl; }
-        }
-        const int total_s = (int)__shfl_sync(0xffffffffu, is, 31), total_l = (int)__shfl_sync(0xffffffffu, il, 31);
-        const int off_s = (int)__shfl_sync(0xffffffffu, is - cs, warp), off_l = (int)__shfl_sync(0xffffffffu, il - cl, warp);
+        if (lane == 0) s_cnt[0][warp] = (unsigned)__popc(ms) | ((unsigned)__popc(ml) << 16);
+        act_sync();   // everyone has read slo/shi/snn; the counts are in
+        const unsigned c = lane < n_act ? s_cnt[0][lane] : 0u;
+        const unsigned tot = __reduce_add_sync(0xffffffffu, c), before = __reduce_add_sync(0xffffffffu, lane < warp ? c : 0u);
+        const int total_s = (int)(tot & 0xffffu), total_l = (int)(tot >> 16);
+        const int off_s = (int)(before & 0xffffu), off_l = (int)(before >> 16);
         if (survive) {
             const int pos = off_s + __popc(ms & lt_mask);
             if (left) {
@@ -259,12 +265,12 @@ __global__ void __launch_bounds__(PLOC_FINISH) ploc_finish_kernel(PlocState* st,
             }
             slo[pos + PLOC_RADIUS] = alo; shi[pos + PLOC_RADIUS] = ahi;
         }
-        __syncthreads();
+        act_sync();
         if (total_s >= m || ++rounds > PLOC_MAX_ITERS) { if (i == 0) st->error = 1; return; }
         m = total_s; node_base += total_l;
     }
     if (i == 0) {
-        st->m = m; st->node_base = node_base;
+        st->m = m; st->node_base = node_base; st->finish_rounds = rounds;
         root_box[0] = slo[PLOC_RADIUS].x; root_box[1] = slo[PLOC_RADIUS].y; root_box[2] = slo[PLOC_RADIUS].z;
         root_box[3] = shi[PLOC_RADIUS].x; root_box[4] = shi[PLOC_RADIUS].y; root_box[5] = shi[PLOC_RADIUS].z;
     }
@@ -318,6 +324,7 @@ int ploc_build(SceneBuffers& sb, cudaStream_t stream, int* launches, bool init_w
 bool ploc_ok(const SceneBuffers& sb, cudaError_t* err) {
     PlocState h{};
     *err = cudaMemcpy(&h, sb.ploc_state, sizeof(h), cudaMemcpyDeviceToHost);
+    if (getenv("MCPT_DIAG_PLOC")) std::fprintf(stderr, "[diag] PLOC: %d grid rounds + %d finish rounds\n", h.rounds & 0x3fffffff, h.finish_rounds);
     return *err == cudaSuccess && h.error == 0 && h.m == 1;
 }
 
