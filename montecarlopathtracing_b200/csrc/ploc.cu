@@ -52,9 +52,11 @@ __device__ __forceinline__ int ploc_nearest(const float4* __restrict__ slo, cons
     for (int off = -PLOC_RADIUS; off <= PLOC_RADIUS; off++) {
         if (off == 0) continue;
         const int j = i + off;
-        if (j < 0 || j >= m) continue;
+        // no branch on the range test: the sixteen box loads are independent and issue back to back (slo/shi extend RADIUS entries
+        // beyond the clusters on either side, so an out-of-range neighbour reads stale but addressable memory and is masked)
+        const bool in_range = j >= 0 && j < m;
         const float a = merged_area(alo, ahi, slo[at + off], shi[at + off]);
-        if (a < best || (a == best && j == (i ^ 1))) { best = a; bj = j; }   // strict <: ties keep the lowest index, but for the buddy
+        if (in_range && (a < best || (a == best && j == (i ^ 1)))) { best = a; bj = j; }   // strict <: ties keep the lowest index, but for the buddy
     }
     return bj;
 }
